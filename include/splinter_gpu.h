@@ -1,0 +1,203 @@
+/*
+ * splinter_gpu.h -- C ABI of libsplinter_gpu.so: the B200 (sm_100a) drop-in for
+ * libsplinter's one data-parallel hot path, the brute-force similarity / distance
+ * scan over per-slot embeddings with the 64-bit bloom-label pre-filter.
+ *
+ * The reference has no library-level search call: the whole path lives in its CLI
+ * command (splinter_cli_cmd_search.c:136-486) on top of five store calls.  This
+ * header therefore DEFINES the search entry points, with the reference's semantics:
+ *
+ *   reference (file:line)                                  replaced by
+ *   ------------------------------------------------------ -------------------------
+ *   splinter_open + static H/S/VALUES (splinter.c:46-57,   spl_gpu_attach / _attach_image
+ *     235-248), magic/version gate (:246)
+ *   splinter_get_slot_snapshot seqlock copy (:532-564),     spl_gpu_sync
+ *     splinter_get_embedding (:590-609), dirty tracking of
+ *     the writers in splinter.c:326-429,567-588,799-867
+ *   splinter_enumerate_matches (:977-989), splinter_list    spl_gpu_search (bloom_mask)
+ *     (:466-477)
+ *   cosine_similarity / euclidean_distance /                spl_gpu_search
+ *     compare_results + qsort + limit + thresholds
+ *     (splinter_cli_cmd_search.c:43-72,373-416)
+ *   search_result_t (_search.c:26-35)                       spl_gpu_result
+ *
+ * Conventions follow splinter.h:398-412: 0 = ok, -1 = recoverable (errno set:
+ * EAGAIN, ENOMEM, EIO for CUDA failures, ...), -2 = caller error (errno = EINVAL).
+ * spl_gpu_last_error() returns a thread-local message for the last failure.
+ *
+ * There is NO CPU fallback: every entry point fails loudly when no sm_100 device
+ * (or no CUDA driver) is present.
+ */
+#ifndef SPLINTER_GPU_H
+#define SPLINTER_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPL_GPU_ABI_VERSION 1
+
+typedef struct spl_gpu_ctx spl_gpu_ctx;
+
+/* ---- result ordering -------------------------------------------------------------- */
+#define SPL_ORDER_COSINE 0u /* reference: similarity desc, then distance asc (_search.c:64-72);
+                               remaining ties (unspecified by the reference's qsort) -> slot idx asc */
+#define SPL_ORDER_L2     1u /* distance asc, similarity desc, idx asc (batched L2 config) */
+
+/* ---- compute mode ------------------------------------------------------------------ */
+#define SPL_MODE_AUTO    0u /* nq < SPL_BATCH_MIN: EXACT; otherwise BATCH_BF16 when a bf16 mirror exists */
+#define SPL_MODE_FAST    1u /* fp32, per-lane partial sums + warp-shuffle tree (|d sim| ~1e-6)           */
+#define SPL_MODE_EXACT   2u /* fp32, the reference's sequential summation order: bit-identical scores   */
+#define SPL_MODE_BATCH_BF16 3u /* tcgen05 Q x E^T on the bf16 mirror, fp32 accumulate, fp32 re-rank     */
+
+/* ---- attach options ---------------------------------------------------------------- */
+#define SPL_OPT_PERSISTENT   0x1u /* name is a file path (open), not a shm name (shm_open): splinter.c:237-241 */
+#define SPL_OPT_BF16_MIRROR  0x2u /* also keep a bf16 copy + fp32 row norms for SPL_MODE_BATCH_BF16            */
+
+typedef struct spl_gpu_opts {
+    uint32_t struct_size;   /* = sizeof(spl_gpu_opts) */
+    int32_t  device;        /* CUDA ordinal; -1 = current device */
+    uint32_t flags;         /* SPL_OPT_* */
+    uint32_t slot_begin;    /* shard: first slot mirrored by this context */
+    uint32_t slot_count;    /* shard: number of slots (0 = to the end of the store) */
+    uint32_t sync_threads;  /* host threads for the snapshot sweep (0 = auto) */
+} spl_gpu_opts;
+
+/* ---- search parameters -------------------------------------------------------------- */
+#define SPL_NO_SLOT 0xFFFFFFFFu
+
+typedef struct spl_gpu_search_params {
+    uint32_t struct_size;    /* = sizeof(spl_gpu_search_params) */
+    uint32_t nq;             /* number of query vectors */
+    uint32_t dim;            /* must equal the mirror's dimension */
+    uint32_t k;              /* --limit; 0 = unlimited like the reference's default (_search.c:415-416) */
+    uint32_t order;          /* SPL_ORDER_* */
+    uint32_t mode;           /* SPL_MODE_* */
+    uint64_t bloom_mask;     /* --bloom; 0 -> splinter_list candidates, else enumerate_matches (_search.c:337-347) */
+    float    min_similarity; /* --similarity; <= 0 disables (_search.c:398) */
+    float    max_distance;   /* --distance;   <= 0 disables (_search.c:399) */
+    uint32_t exclude_slot;   /* slot of the caller's scratch key (_search.c:367); SPL_NO_SLOT = none.
+                                Index is GLOBAL (store slot index), like every index in this API. */
+    uint32_t reserved;
+} spl_gpu_search_params;
+
+/* One hit.  Mirrors search_result_t (_search.c:26-35) with the key replaced by its slot index
+ * (slot_ptr - S); key / val_len / type are resolved from the store by the host caller. */
+typedef struct spl_gpu_result {
+    uint32_t slot_idx;       /* global slot index */
+    float    similarity;
+    float    distance;       /* FLT_MAX when has_embedding == 0 (_search.c:388-391) */
+    uint32_t has_embedding;
+    uint64_t epoch;          /* slot epoch of the mirrored snapshot */
+    uint64_t bloom;
+} spl_gpu_result;
+
+typedef struct spl_gpu_sync_stats {
+    uint64_t generation;     /* snapshot id after this sync */
+    uint64_t slots_swept;
+    uint64_t rows_uploaded;  /* embedding rows re-sent (dirty {hash,epoch} or first sync) */
+    uint64_t meta_updated;   /* bloom / validity-only updates (set_label moves no slot epoch) */
+    uint64_t skipped_busy;   /* odd epoch or torn copy: previous mirror row kept, retried next sync */
+    uint64_t aba_rechecked;  /* epoch-4 rows re-validated by content after retrain's backward epoch */
+    uint64_t bytes_h2d;
+    double   sweep_ms, upload_ms;
+    uint64_t header_epoch;   /* H->epoch observed at the start of the sweep */
+} spl_gpu_sync_stats;
+
+typedef struct spl_gpu_info {
+    uint32_t abi_version, dim;
+    uint64_t total_slots;    /* store geometry (H->slots) or dense rows */
+    uint64_t slot_begin, slot_count;
+    uint64_t generation;
+    int32_t  device, sm_count;
+    uint32_t has_bf16_mirror, is_dense;
+    uint64_t hbm_bytes;      /* device memory held by this context */
+} spl_gpu_info;
+
+/* ---- lifecycle ---------------------------------------------------------------------- */
+
+/* Map the store `name_or_path` read-only (same shm name / file the reference opens:
+ * splinter.c:235-248), check magic/version (:246) and that the per-slot size equals
+ * 128 + 4*D for some D (SURVEY 8(b) geometry gate), allocate the HBM mirror, and run a
+ * first full spl_gpu_sync.  NULL on failure (errno + spl_gpu_last_error). */
+spl_gpu_ctx *spl_gpu_attach(const char *name_or_path, const spl_gpu_opts *opts);
+
+/* Same over a store image the caller has already mapped (e.g. the mapping the reference
+ * library itself made).  The memory must stay mapped until spl_gpu_detach. */
+spl_gpu_ctx *spl_gpu_attach_image(const void *base, size_t size, const spl_gpu_opts *opts);
+
+/* A device-only shard with no backing store: n_rows x dim fp32 rows plus bloom / flags /
+ * epoch columns, filled by spl_gpu_dense_upload or spl_gpu_dense_fill_synthetic.  Used for
+ * geometries one store cannot express (D != 768, > 4 GiB arenas: splinter.h:39,194,235). */
+spl_gpu_ctx *spl_gpu_open_dense(uint64_t n_rows, uint32_t dim, uint64_t global_row0, const spl_gpu_opts *opts);
+
+void spl_gpu_detach(spl_gpu_ctx *ctx);
+
+int  spl_gpu_get_info(const spl_gpu_ctx *ctx, spl_gpu_info *out);
+const char *spl_gpu_last_error(void);
+
+/* ---- mirror maintenance ------------------------------------------------------------- */
+
+/* Sweep the store and re-upload only dirty slots.  A slot is copied only while its seqlock
+ * epoch is even and unchanged across the copy (reader rule, splinter.c:598-605); a slot that
+ * is busy keeps its previous mirror row and is counted in skipped_busy.  Dirty = cached
+ * {hash, epoch, bloom, val_len>0} differs from the slot's (label changes move no slot epoch:
+ * splinter.c:843).  May run concurrently with spl_gpu_search from other threads. */
+int spl_gpu_sync(spl_gpu_ctx *ctx, spl_gpu_sync_stats *stats /* nullable */);
+
+/* dense contexts: copy rows [first_row, first_row+n_rows) from host arrays.  flags bits are
+ * SPL_ROW_*; bloom/flags/epoch may be NULL (-> 0 / all candidate bits / 2). */
+#define SPL_ROW_LIST 0x01u /* splinter_list candidate:      hash!=0 && val_len>0 && epoch!=0 && key[0] */
+#define SPL_ROW_ENUM 0x02u /* enumerate_matches candidate:  hash!=0 && epoch!=0 && key[0]              */
+#define SPL_ROW_EMB  0x04u /* a consistent embedding copy exists (else sim=0, dist=FLT_MAX)            */
+int spl_gpu_dense_upload(spl_gpu_ctx *ctx, uint64_t first_row, uint64_t n_rows, const float *E,
+                         const uint64_t *bloom, const uint8_t *flags, const uint64_t *epoch);
+
+/* dense contexts: generate SURVEY 8(d)'s synthetic corpus on the device (counter RNG keyed by
+ * (seed, global row, d); bit-identical to the oracle's generator). */
+int spl_gpu_dense_fill_synthetic(spl_gpu_ctx *ctx, uint64_t seed_corpus, uint64_t seed_bloom);
+
+/* read back mirror rows (tests / debugging): any output pointer may be NULL */
+int spl_gpu_read_mirror(spl_gpu_ctx *ctx, uint64_t first_slot, uint64_t n, float *E,
+                        uint64_t *bloom, uint8_t *flags, uint64_t *epoch);
+
+/* ---- search ------------------------------------------------------------------------- */
+
+/* Host-buffer search (the reference-facing call).  q = nq x dim fp32.  out = nq x out_stride
+ * records; out_stride >= k when k > 0.  counts[nq] receives the number of hits per query
+ * (<= k; fewer when fewer candidates survive).  With k == 0 the call returns every survivor,
+ * sorted, up to out_stride per query, and counts[] holds the TOTAL number of survivors (which
+ * may exceed out_stride: call again with a larger buffer).
+ * Results per query are sorted by p->order. */
+int spl_gpu_search(spl_gpu_ctx *ctx, const spl_gpu_search_params *p, const float *q,
+                   spl_gpu_result *out, uint32_t out_stride, uint32_t *counts);
+
+/* Device-buffer search: d_q / d_out / d_counts are device pointers on the context's device;
+ * the launches are enqueued on `stream` (a cudaStream_t; NULL = the context's stream) and the
+ * call does not synchronise.  k must be in 1..SPL_GPU_KMAX_FUSED. */
+#define SPL_GPU_KMAX_FUSED 256u
+int spl_gpu_search_device(spl_gpu_ctx *ctx, const spl_gpu_search_params *p, const float *d_q,
+                          spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, void *stream);
+
+/* Merge per-shard result lists (already sorted or not) into the global top-k on the device:
+ * d_lists = nlists x list_stride records, d_counts[nlists].  Used after the all-gather of the
+ * per-GPU local top-k.  Enqueued on `stream`, no synchronisation. */
+int spl_gpu_merge_topk_device(spl_gpu_ctx *ctx, const spl_gpu_result *d_lists, const uint32_t *d_counts,
+                              uint32_t nlists, uint32_t list_stride, uint32_t order, uint32_t k,
+                              spl_gpu_result *d_out, uint32_t *d_out_count, void *stream);
+
+/* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
+uint64_t spl_gpu_launch_count(const spl_gpu_ctx *ctx);
+
+/* last kernel's device time of the most recent spl_gpu_search in ms (CUDA events on the
+ * context's stream), or < 0 if timing is off.  Enable with spl_gpu_set_timing(ctx, 1). */
+int    spl_gpu_set_timing(spl_gpu_ctx *ctx, int on);
+double spl_gpu_last_scan_ms(const spl_gpu_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLINTER_GPU_H */

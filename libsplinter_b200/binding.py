@@ -1,0 +1,242 @@
+"""ctypes binding of libsplinter_gpu.so (C ABI: include/splinter_gpu.h).
+
+This is the harness-side view used by tests/, bench.py and __graft_entry__.py; the product is
+the shared library itself.  There is no CPU fallback: if the library is missing the import of
+this module raises, and every entry point fails loudly without a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "libsplinter_gpu.so"
+
+# symbols include/splinter_gpu.h declares; tests check every one is exported
+ABI_SYMBOLS = [
+    "spl_gpu_attach", "spl_gpu_attach_image", "spl_gpu_open_dense", "spl_gpu_detach", "spl_gpu_get_info",
+    "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
+    "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device",
+    "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms",
+]
+
+ORDER_COSINE, ORDER_L2 = 0, 1
+MODE_AUTO, MODE_FAST, MODE_EXACT, MODE_BATCH_BF16 = 0, 1, 2, 3
+OPT_PERSISTENT, OPT_BF16_MIRROR = 0x1, 0x2
+ROW_LIST, ROW_ENUM, ROW_EMB = 0x1, 0x2, 0x4
+NO_SLOT = 0xFFFFFFFF
+KMAX_FUSED = 256
+
+
+class Opts(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("flags", C.c_uint32),
+                ("slot_begin", C.c_uint32), ("slot_count", C.c_uint32), ("sync_threads", C.c_uint32)]
+
+
+class SearchParams(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("nq", C.c_uint32), ("dim", C.c_uint32), ("k", C.c_uint32),
+                ("order", C.c_uint32), ("mode", C.c_uint32), ("bloom_mask", C.c_uint64),
+                ("min_similarity", C.c_float), ("max_distance", C.c_float), ("exclude_slot", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+
+class SyncStats(C.Structure):
+    _fields_ = [("generation", C.c_uint64), ("slots_swept", C.c_uint64), ("rows_uploaded", C.c_uint64),
+                ("meta_updated", C.c_uint64), ("skipped_busy", C.c_uint64), ("aba_rechecked", C.c_uint64),
+                ("bytes_h2d", C.c_uint64), ("sweep_ms", C.c_double), ("upload_ms", C.c_double),
+                ("header_epoch", C.c_uint64)]
+
+
+class Info(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("dim", C.c_uint32), ("total_slots", C.c_uint64),
+                ("slot_begin", C.c_uint64), ("slot_count", C.c_uint64), ("generation", C.c_uint64),
+                ("device", C.c_int32), ("sm_count", C.c_int32), ("has_bf16_mirror", C.c_uint32),
+                ("is_dense", C.c_uint32), ("hbm_bytes", C.c_uint64)]
+
+
+RESULT_DTYPE = np.dtype([("slot_idx", "<u4"), ("similarity", "<f4"), ("distance", "<f4"),
+                         ("has_embedding", "<u4"), ("epoch", "<u8"), ("bloom", "<u8")])
+assert RESULT_DTYPE.itemsize == 32
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen the in-tree library (built by __graft_entry__.build()).  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(str(LIB_PATH), mode=os.RTLD_GLOBAL if hasattr(os, "RTLD_GLOBAL") else 0)
+    vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+    lib.spl_gpu_attach.restype = vp
+    lib.spl_gpu_attach.argtypes = [C.c_char_p, C.POINTER(Opts)]
+    lib.spl_gpu_attach_image.restype = vp
+    lib.spl_gpu_attach_image.argtypes = [vp, C.c_size_t, C.POINTER(Opts)]
+    lib.spl_gpu_open_dense.restype = vp
+    lib.spl_gpu_open_dense.argtypes = [u64, u32, u64, C.POINTER(Opts)]
+    lib.spl_gpu_detach.restype = None
+    lib.spl_gpu_detach.argtypes = [vp]
+    lib.spl_gpu_get_info.restype = C.c_int
+    lib.spl_gpu_get_info.argtypes = [vp, C.POINTER(Info)]
+    lib.spl_gpu_last_error.restype = C.c_char_p
+    lib.spl_gpu_last_error.argtypes = []
+    lib.spl_gpu_sync.restype = C.c_int
+    lib.spl_gpu_sync.argtypes = [vp, C.POINTER(SyncStats)]
+    lib.spl_gpu_dense_upload.restype = C.c_int
+    lib.spl_gpu_dense_upload.argtypes = [vp, u64, u64, vp, vp, vp, vp]
+    lib.spl_gpu_dense_fill_synthetic.restype = C.c_int
+    lib.spl_gpu_dense_fill_synthetic.argtypes = [vp, u64, u64]
+    lib.spl_gpu_read_mirror.restype = C.c_int
+    lib.spl_gpu_read_mirror.argtypes = [vp, u64, u64, vp, vp, vp, vp]
+    lib.spl_gpu_search.restype = C.c_int
+    lib.spl_gpu_search.argtypes = [vp, C.POINTER(SearchParams), vp, vp, u32, vp]
+    lib.spl_gpu_search_device.restype = C.c_int
+    lib.spl_gpu_search_device.argtypes = [vp, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
+    lib.spl_gpu_merge_topk_device.restype = C.c_int
+    lib.spl_gpu_merge_topk_device.argtypes = [vp, vp, vp, u32, u32, u32, u32, vp, vp, vp]
+    lib.spl_gpu_launch_count.restype = u64
+    lib.spl_gpu_launch_count.argtypes = [vp]
+    lib.spl_gpu_set_timing.restype = C.c_int
+    lib.spl_gpu_set_timing.argtypes = [vp, C.c_int]
+    lib.spl_gpu_last_scan_ms.restype = C.c_double
+    lib.spl_gpu_last_scan_ms.argtypes = [vp]
+    _lib = lib
+    return lib
+
+
+class SplinterGpuError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _opts(device=-1, flags=0, slot_begin=0, slot_count=0, sync_threads=0):
+    return Opts(C.sizeof(Opts), device, flags, slot_begin, slot_count, sync_threads)
+
+
+class Mirror:
+    """One HBM mirror context (a store shard or a dense device-only shard)."""
+
+    def __init__(self, handle):
+        self._lib = load()
+        if not handle:
+            raise SplinterGpuError(self._lib.spl_gpu_last_error().decode() or "attach failed")
+        self._h = C.c_void_p(handle)
+        self._keep = None
+
+    # ---- constructors ----
+    @classmethod
+    def attach(cls, name_or_path: str, **kw):
+        lib = load()
+        o = _opts(**kw)
+        return cls(lib.spl_gpu_attach(name_or_path.encode(), C.byref(o)))
+
+    @classmethod
+    def attach_image(cls, image: np.ndarray, **kw):
+        lib = load()
+        o = _opts(**kw)
+        assert image.dtype == np.uint8 and image.flags.c_contiguous
+        m = cls(lib.spl_gpu_attach_image(_ptr(image), image.nbytes, C.byref(o)))
+        m._keep = image
+        return m
+
+    @classmethod
+    def open_dense(cls, n_rows: int, dim: int, global_row0: int = 0, **kw):
+        lib = load()
+        o = _opts(**kw)
+        return cls(lib.spl_gpu_open_dense(n_rows, dim, global_row0, C.byref(o)))
+
+    # ---- plumbing ----
+    def _check(self, rc):
+        if rc != 0:
+            raise SplinterGpuError(f"rc={rc} errno={C.get_errno()}: {self._lib.spl_gpu_last_error().decode()}")
+
+    def close(self):
+        if self._h:
+            self._lib.spl_gpu_detach(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def handle(self):
+        return self._h
+
+    def info(self) -> Info:
+        i = Info()
+        self._check(self._lib.spl_gpu_get_info(self._h, C.byref(i)))
+        return i
+
+    def sync(self) -> SyncStats:
+        s = SyncStats()
+        self._check(self._lib.spl_gpu_sync(self._h, C.byref(s)))
+        return s
+
+    def dense_upload(self, first_row, E, bloom=None, flags=None, epoch=None):
+        E = np.ascontiguousarray(E, dtype=np.float32)
+        n = E.shape[0]
+        bloom = None if bloom is None else np.ascontiguousarray(bloom, dtype=np.uint64)
+        flags = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint8)
+        epoch = None if epoch is None else np.ascontiguousarray(epoch, dtype=np.uint64)
+        self._check(self._lib.spl_gpu_dense_upload(self._h, first_row, n, _ptr(E), _ptr(bloom), _ptr(flags), _ptr(epoch)))
+
+    def fill_synthetic(self, seed_corpus=1234, seed_bloom=99):
+        self._check(self._lib.spl_gpu_dense_fill_synthetic(self._h, seed_corpus, seed_bloom))
+
+    def read_mirror(self, first_slot, n, want_E=True):
+        dim = self.info().dim
+        E = np.empty((n, dim), np.float32) if want_E else None
+        bloom = np.empty(n, np.uint64)
+        flags = np.empty(n, np.uint8)
+        epoch = np.empty(n, np.uint64)
+        self._check(self._lib.spl_gpu_read_mirror(self._h, first_slot, n, _ptr(E), _ptr(bloom), _ptr(flags), _ptr(epoch)))
+        return E, bloom, flags, epoch
+
+    def params(self, nq, k, order=ORDER_COSINE, mode=MODE_AUTO, bloom_mask=0, min_similarity=0.0,
+               max_distance=0.0, exclude_slot=NO_SLOT) -> SearchParams:
+        return SearchParams(C.sizeof(SearchParams), nq, self.info().dim, k, order, mode, bloom_mask,
+                            min_similarity, max_distance, exclude_slot, 0)
+
+    def search(self, q, k, out_stride=None, **kw):
+        """Host-buffer search.  Returns (results[nq, stride] structured array, counts[nq])."""
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        nq = q.shape[0]
+        p = self.params(nq, k, **kw)
+        p.dim = q.shape[1]  # a wrong dimension must be rejected by the library, not papered over here
+        stride = out_stride if out_stride is not None else (k if k > 0 else int(self.info().slot_count))
+        out = np.zeros((nq, stride), RESULT_DTYPE)
+        counts = np.zeros(nq, np.uint32)
+        self._check(self._lib.spl_gpu_search(self._h, C.byref(p), _ptr(q), _ptr(out), stride, _ptr(counts)))
+        return out, counts
+
+    def search_device(self, p: SearchParams, d_q: int, d_out: int, out_stride: int, d_counts: int, stream: int = 0):
+        self._check(self._lib.spl_gpu_search_device(self._h, C.byref(p), C.c_void_p(d_q), C.c_void_p(d_out),
+                                                    out_stride, C.c_void_p(d_counts), C.c_void_p(stream)))
+
+    def merge_topk_device(self, d_lists, d_counts, nlists, stride, order, k, d_out, d_out_count, stream=0):
+        self._check(self._lib.spl_gpu_merge_topk_device(self._h, C.c_void_p(d_lists), C.c_void_p(d_counts), nlists,
+                                                        stride, order, k, C.c_void_p(d_out), C.c_void_p(d_out_count),
+                                                        C.c_void_p(stream)))
+
+    def launch_count(self) -> int:
+        return int(self._lib.spl_gpu_launch_count(self._h))
+
+    def set_timing(self, on=True):
+        self._check(self._lib.spl_gpu_set_timing(self._h, int(on)))
+
+    def last_scan_ms(self) -> float:
+        return float(self._lib.spl_gpu_last_scan_ms(self._h))

@@ -1,0 +1,729 @@
+// spl_host.cu -- host side of libsplinter_gpu.so: the C ABI declared in include/splinter_gpu.h.
+//
+//  * attach: map the reference's store (same shm name / file as splinter_open,
+//    /root/reference/splinter.c:235-248), gate on magic/version (:246) and slot geometry;
+//  * sync:   epoch-consistent snapshot of the slot array into HBM.  A slot is copied only while
+//    its seqlock epoch is even and unchanged over the copy (reader rule, splinter.c:598-605);
+//    only slots whose cached {hash, epoch, bloom, validity} moved are re-sent (writers:
+//    splinter.c:326-429, 567-588, 799-867);
+//  * search: launches the sm_100a kernels (spl_scan.cu, spl_exact.cu, spl_batch.cu).
+//
+// No CPU fallback exists: without a CUDA device every entry point fails with errno = EIO.
+#include <errno.h>
+#include <fcntl.h>
+#include <float.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <chrono>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "spl_mirror.cuh"
+#include "spl_scan.cuh"
+
+using namespace spl;
+
+// ---- store layout (splinter.h:176-255; offsets measured with offsetof on the reference) --------
+namespace layout {
+constexpr uint32_t kMagic = 0x534C4E54u, kVersion = 4u;
+constexpr size_t kHeaderSize = 5440, kSlotMeta = 128;
+constexpr size_t H_MAGIC = 0, H_VERSION = 4, H_SLOTS = 8, H_MAXVAL = 12, H_EPOCH = 16;
+constexpr size_t S_HASH = 0, S_EPOCH = 8, S_VAL_LEN = 20, S_BLOOM = 56, S_KEY = 64, S_EMBED = 128;
+}  // namespace layout
+
+static thread_local char g_err[512] = "";
+
+static int fail(int rc, int err, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    errno = err;
+    return rc;
+}
+#define CUDA_TRY(expr)                                                                                   \
+    do {                                                                                                 \
+        cudaError_t e__ = (expr);                                                                        \
+        if (e__ != cudaSuccess) return fail(-1, EIO, "%s failed: %s", #expr, cudaGetErrorString(e__));   \
+    } while (0)
+
+struct StageBuf {
+    float *h_rows = nullptr, *d_rows = nullptr;
+    StagedMeta *h_meta = nullptr, *d_meta = nullptr;
+    uint32_t cap = 0, n = 0;
+    cudaEvent_t ev = nullptr;
+    bool in_flight = false;
+};
+
+struct spl_gpu_ctx {
+    int device = 0, sm_count = 0;
+    cudaStream_t stream = nullptr;
+    // store mapping
+    const uint8_t *base = nullptr;
+    size_t map_size = 0;
+    bool own_map = false;
+    uint64_t total_slots = 0;
+    uint32_t dim = 0;
+    size_t slot_size = 0;
+    uint64_t slot_begin = 0, n = 0;  // shard: local row r <-> global slot slot_begin + r
+    bool dense = false;
+    uint32_t sync_threads = 0;
+    // device mirror
+    MirrorPtrs m{};
+    uint64_t hbm_bytes = 0;
+    // host caches for dirty detection (store-backed contexts)
+    std::vector<uint64_t> c_hash, c_epoch, c_bloom;
+    std::vector<uint8_t> c_flags;   // SPL_ROW_* incl. EMB
+    std::vector<uint8_t> c_state;   // bit0: mirrored at least once, bit1: mirrored row is non-zero
+    uint64_t c_header_epoch = 0;
+    bool first_sync = true;
+    std::atomic<uint64_t> generation{0};
+    // per-sync-thread staging (2 row buffers + 2 meta buffers each)
+    std::vector<StageBuf> stage;
+    uint32_t stage_rows = 0, stage_meta = 0;
+    // search scratch
+    int scan_grid = 0;
+    Cand *d_cands = nullptr;
+    uint32_t *d_counters = nullptr;
+    float *d_q = nullptr, *h_q = nullptr;
+    spl_gpu_result *d_out = nullptr, *h_out = nullptr;
+    uint32_t *d_count = nullptr, *h_count = nullptr;
+    uint32_t q_cap = 0, out_cap = 0;
+    // unlimited-k scratch (lazy)
+    uint64_t *d_keys = nullptr;
+    void *d_sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+    spl_gpu_result *d_big_out = nullptr;
+    uint32_t big_out_cap = 0;
+    float *d_synth_scale = nullptr;
+    // bookkeeping
+    std::mutex mu;  // serialises enqueueing on `stream` and the scratch above
+    std::atomic<uint64_t> launches{0};
+    bool timing = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double last_scan_ms = -1.0;
+};
+
+static constexpr uint32_t kMaxBatchQ = 4096;
+
+// ------------------------------------------------------------------------------------------------
+static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(-1, EIO, "no CUDA device (%s); libsplinter_gpu has no CPU fallback", cudaGetErrorString(e));
+    int dev = (o && o->device >= 0) ? o->device : -1;
+    if (dev < 0) CUDA_TRY(cudaGetDevice(&dev));
+    if (dev >= ndev) return fail(-2, EINVAL, "device %d out of range (%d devices)", dev, ndev);
+    CUDA_TRY(cudaSetDevice(dev));
+    cudaDeviceProp p;
+    CUDA_TRY(cudaGetDeviceProperties(&p, dev));
+    if (p.major < 10)
+        return fail(-1, EIO, "device %d is sm_%d%d; this library carries sm_100a code only", dev, p.major, p.minor);
+    c->device = dev;
+    c->sm_count = p.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreate(&c->ev0));
+    CUDA_TRY(cudaEventCreate(&c->ev1));
+    return 0;
+}
+
+template <typename T>
+static int dev_alloc(spl_gpu_ctx *c, T **p, size_t count, bool zero) {
+    size_t bytes = count * sizeof(T);
+    if (bytes == 0) bytes = sizeof(T);
+    cudaError_t e = cudaMalloc((void **)p, bytes);
+    if (e != cudaSuccess) return fail(-1, ENOMEM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+    c->hbm_bytes += bytes;
+    if (zero) CUDA_TRY(cudaMemsetAsync(*p, 0, bytes, c->stream));
+    return 0;
+}
+
+static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
+    int rc;
+    if ((rc = dev_alloc(c, &c->m.E, c->n * c->dim, true))) return rc;
+    if ((rc = dev_alloc(c, &c->m.bloom, c->n, true))) return rc;
+    if ((rc = dev_alloc(c, &c->m.flags, c->n, true))) return rc;
+    if ((rc = dev_alloc(c, &c->m.epoch, c->n, true))) return rc;
+    if (bf16) {
+        if ((rc = dev_alloc(c, &c->m.E16, c->n * c->dim, true))) return rc;
+        if ((rc = dev_alloc(c, &c->m.norm2, c->n, true))) return rc;
+    }
+    c->m.dim = c->dim;
+    // search scratch
+    c->scan_grid = c->sm_count * scan_fast_ctas_per_sm(c->dim, 0);
+    if ((rc = dev_alloc(c, &c->d_cands, (size_t)c->scan_grid * SPL_GPU_KMAX_FUSED, false))) return rc;
+    if ((rc = dev_alloc(c, &c->d_counters, 8, true))) return rc;
+    c->q_cap = 64;
+    c->out_cap = 64 * SPL_GPU_KMAX_FUSED;
+    if ((rc = dev_alloc(c, &c->d_q, (size_t)c->q_cap * c->dim, false))) return rc;
+    if ((rc = dev_alloc(c, &c->d_out, c->out_cap, false))) return rc;
+    if ((rc = dev_alloc(c, &c->d_count, c->q_cap, true))) return rc;
+    CUDA_TRY(cudaMallocHost((void **)&c->h_q, (size_t)c->q_cap * c->dim * sizeof(float)));
+    CUDA_TRY(cudaMallocHost((void **)&c->h_out, (size_t)c->out_cap * sizeof(spl_gpu_result)));
+    CUDA_TRY(cudaMallocHost((void **)&c->h_count, (size_t)c->q_cap * sizeof(uint32_t)));
+    // staging for sync / dense upload
+    if (c->sync_threads == 0) {
+        unsigned hc = std::thread::hardware_concurrency();
+        c->sync_threads = hc ? (hc > 16 ? 16 : hc) : 4;
+    }
+    const size_t row_bytes = (size_t)c->dim * 4;
+    c->stage_rows = (uint32_t)((8u << 20) / row_bytes);
+    if (c->stage_rows < 64) c->stage_rows = 64;
+    c->stage_meta = 32768;
+    c->stage.resize((size_t)c->sync_threads * 4);
+    for (size_t i = 0; i < c->stage.size(); i++) {
+        StageBuf &b = c->stage[i];
+        const bool rows = (i & 2) == 0;  // per thread: [0,1] row buffers, [2,3] meta-only buffers
+        b.cap = rows ? c->stage_rows : c->stage_meta;
+        if (rows) {
+            CUDA_TRY(cudaMallocHost((void **)&b.h_rows, (size_t)b.cap * row_bytes));
+            if ((rc = dev_alloc(c, &b.d_rows, (size_t)b.cap * c->dim, false))) return rc;
+        }
+        CUDA_TRY(cudaMallocHost((void **)&b.h_meta, (size_t)b.cap * sizeof(StagedMeta)));
+        if ((rc = dev_alloc(c, &b.d_meta, b.cap, false))) return rc;
+        CUDA_TRY(cudaEventCreateWithFlags(&b.ev, cudaEventDisableTiming));
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+static void destroy(spl_gpu_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    cudaFree(c->m.E); cudaFree(c->m.bloom); cudaFree(c->m.flags); cudaFree(c->m.epoch);
+    cudaFree(c->m.E16); cudaFree(c->m.norm2);
+    cudaFree(c->d_cands); cudaFree(c->d_counters); cudaFree(c->d_q); cudaFree(c->d_out); cudaFree(c->d_count);
+    cudaFree(c->d_keys); cudaFree(c->d_sort_tmp); cudaFree(c->d_big_out); cudaFree(c->d_synth_scale);
+    cudaFreeHost(c->h_q); cudaFreeHost(c->h_out); cudaFreeHost(c->h_count);
+    for (StageBuf &b : c->stage) {
+        cudaFreeHost(b.h_rows); cudaFreeHost(b.h_meta); cudaFree(b.d_rows); cudaFree(b.d_meta);
+        if (b.ev) cudaEventDestroy(b.ev);
+    }
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->own_map && c->base) munmap((void *)c->base, c->map_size);
+    delete c;
+}
+
+// ---- geometry gate: slot size must be 128 + 4*D ------------------------------------
+static int parse_geometry(spl_gpu_ctx *c, const uint8_t *base, size_t size) {
+    using namespace layout;
+    if (size < kHeaderSize) return fail(-1, EINVAL, "mapping smaller than a splinter header");
+    uint32_t magic, version, slots, maxval;
+    memcpy(&magic, base + H_MAGIC, 4); memcpy(&version, base + H_VERSION, 4);
+    memcpy(&slots, base + H_SLOTS, 4); memcpy(&maxval, base + H_MAXVAL, 4);
+    if (magic != kMagic || version != kVersion)
+        return fail(-1, EINVAL, "not a splinter v%u store (magic %08x version %u)", kVersion, magic, version);
+    if (slots == 0) return fail(-1, EINVAL, "store has no slots");
+    uint64_t rest = size - kHeaderSize, arena = (uint64_t)slots * maxval;
+    if (rest < arena || (rest - arena) % slots) return fail(-1, EINVAL, "store size does not match its header");
+    uint64_t ss = (rest - arena) / slots;
+    if (ss <= kSlotMeta || (ss - kSlotMeta) % 16)
+        return fail(-1, EINVAL, "slot size %llu: store was built without embeddings (need 128 + 4*D)",
+                    (unsigned long long)ss);
+    c->total_slots = slots;
+    c->slot_size = (size_t)ss;
+    c->dim = (uint32_t)((ss - kSlotMeta) / 4);
+    c->base = base;
+    c->map_size = size;
+    return 0;
+}
+
+static spl_gpu_ctx *attach_common(spl_gpu_ctx *c, const spl_gpu_opts *o) {
+    c->slot_begin = o ? o->slot_begin : 0;
+    uint64_t cnt = o ? o->slot_count : 0;
+    if (c->slot_begin >= c->total_slots) { fail(-2, EINVAL, "slot_begin beyond the store"); destroy(c); return nullptr; }
+    if (cnt == 0 || c->slot_begin + cnt > c->total_slots) cnt = c->total_slots - c->slot_begin;
+    c->n = cnt;
+    c->sync_threads = o ? o->sync_threads : 0;
+    if (device_setup(c, o) || alloc_mirror(c, o && (o->flags & SPL_OPT_BF16_MIRROR))) { destroy(c); return nullptr; }
+    c->c_hash.assign(c->n, 0); c->c_epoch.assign(c->n, 0); c->c_bloom.assign(c->n, 0);
+    c->c_flags.assign(c->n, 0); c->c_state.assign(c->n, 0);
+    if (spl_gpu_sync(c, nullptr) != 0) { destroy(c); return nullptr; }
+    return c;
+}
+
+extern "C" spl_gpu_ctx *spl_gpu_attach(const char *name_or_path, const spl_gpu_opts *o) {
+    if (!name_or_path) { fail(-2, EINVAL, "null store name"); return nullptr; }
+    int fd = (o && (o->flags & SPL_OPT_PERSISTENT)) ? open(name_or_path, O_RDONLY) : shm_open(name_or_path, O_RDONLY, 0);
+    if (fd < 0) { fail(-1, errno, "cannot open store '%s': %s", name_or_path, strerror(errno)); return nullptr; }
+    struct stat st;
+    if (fstat(fd, &st) != 0) { int e = errno; close(fd); fail(-1, e, "fstat: %s", strerror(e)); return nullptr; }
+    void *base = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_SHARED, fd, 0);
+    close(fd);
+    if (base == MAP_FAILED) { fail(-1, errno, "mmap: %s", strerror(errno)); return nullptr; }
+    spl_gpu_ctx *c = new spl_gpu_ctx();
+    c->own_map = true;
+    c->base = (const uint8_t *)base;
+    c->map_size = (size_t)st.st_size;
+    if (parse_geometry(c, (const uint8_t *)base, (size_t)st.st_size)) { destroy(c); return nullptr; }
+    return attach_common(c, o);
+}
+
+extern "C" spl_gpu_ctx *spl_gpu_attach_image(const void *base, size_t size, const spl_gpu_opts *o) {
+    if (!base) { fail(-2, EINVAL, "null image"); return nullptr; }
+    spl_gpu_ctx *c = new spl_gpu_ctx();
+    if (parse_geometry(c, (const uint8_t *)base, size)) { destroy(c); return nullptr; }
+    return attach_common(c, o);
+}
+
+extern "C" spl_gpu_ctx *spl_gpu_open_dense(uint64_t n_rows, uint32_t dim, uint64_t global_row0, const spl_gpu_opts *o) {
+    if (n_rows == 0 || n_rows > 0xFFFFFFF0ull || dim == 0 || dim % 4) {
+        fail(-2, EINVAL, "dense shard needs 0 < rows < 2^32 and dim %% 4 == 0");
+        return nullptr;
+    }
+    spl_gpu_ctx *c = new spl_gpu_ctx();
+    c->dense = true;
+    c->dim = dim;
+    c->n = n_rows;
+    c->total_slots = n_rows;
+    c->slot_begin = global_row0;
+    c->sync_threads = o ? o->sync_threads : 0;
+    if (c->sync_threads == 0) c->sync_threads = 2;
+    if (device_setup(c, o) || alloc_mirror(c, o && (o->flags & SPL_OPT_BF16_MIRROR))) { destroy(c); return nullptr; }
+    return c;
+}
+
+extern "C" void spl_gpu_detach(spl_gpu_ctx *c) { destroy(c); }
+
+extern "C" const char *spl_gpu_last_error(void) { return g_err; }
+
+extern "C" int spl_gpu_get_info(const spl_gpu_ctx *c, spl_gpu_info *out) {
+    if (!c || !out) return fail(-2, EINVAL, "null argument");
+    memset(out, 0, sizeof *out);
+    out->abi_version = SPL_GPU_ABI_VERSION;
+    out->dim = c->dim;
+    out->total_slots = c->total_slots;
+    out->slot_begin = c->slot_begin;
+    out->slot_count = c->n;
+    out->generation = c->generation.load();
+    out->device = c->device;
+    out->sm_count = c->sm_count;
+    out->has_bf16_mirror = c->m.E16 != nullptr;
+    out->is_dense = c->dense;
+    out->hbm_bytes = c->hbm_bytes;
+    return 0;
+}
+
+extern "C" uint64_t spl_gpu_launch_count(const spl_gpu_ctx *c) { return c ? c->launches.load() : 0; }
+extern "C" int spl_gpu_set_timing(spl_gpu_ctx *c, int on) {
+    if (!c) return fail(-2, EINVAL, "null context");
+    c->timing = on != 0;
+    return 0;
+}
+extern "C" double spl_gpu_last_scan_ms(const spl_gpu_ctx *c) { return c ? c->last_scan_ms : -1.0; }
+
+// ------------------------------------------------------------------------------------------------
+// sync
+// ------------------------------------------------------------------------------------------------
+struct SyncCounters {
+    std::atomic<uint64_t> rows{0}, meta{0}, busy{0}, aba{0}, bytes{0};
+    std::atomic<int> err{0};
+};
+
+static int flush_buf(spl_gpu_ctx *c, StageBuf &b, bool rows, SyncCounters &sc) {
+    if (b.n == 0) return 0;
+    std::lock_guard<std::mutex> lk(c->mu);
+    const size_t row_bytes = (size_t)c->dim * 4;
+    if (rows) {
+        CUDA_TRY(cudaMemcpyAsync(b.d_rows, b.h_rows, (size_t)b.n * row_bytes, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(b.d_meta, b.h_meta, (size_t)b.n * sizeof(StagedMeta), cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(launch_scatter_rows(c->m, b.d_rows, b.d_meta, b.n, c->sm_count, c->stream));
+        sc.bytes += (uint64_t)b.n * (row_bytes + sizeof(StagedMeta));
+    } else {
+        CUDA_TRY(cudaMemcpyAsync(b.d_meta, b.h_meta, (size_t)b.n * sizeof(StagedMeta), cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(launch_scatter_meta(c->m, b.d_meta, b.n, c->stream));
+        sc.bytes += (uint64_t)b.n * sizeof(StagedMeta);
+    }
+    c->launches++;
+    CUDA_TRY(cudaEventRecord(b.ev, c->stream));
+    b.in_flight = true;
+    b.n = 0;
+    return 0;
+}
+
+static int acquire_buf(StageBuf &b) {
+    if (b.in_flight) {
+        CUDA_TRY(cudaEventSynchronize(b.ev));
+        b.in_flight = false;
+    }
+    b.n = 0;
+    return 0;
+}
+
+static inline uint64_t ld_acq64(const uint8_t *p) { return __atomic_load_n(reinterpret_cast<const uint64_t *>(p), __ATOMIC_ACQUIRE); }
+static inline uint32_t ld_acq32(const uint8_t *p) { return __atomic_load_n(reinterpret_cast<const uint32_t *>(p), __ATOMIC_ACQUIRE); }
+
+static inline uint8_t validity_bits(uint64_t hash, uint64_t epoch, uint32_t val_len, uint8_t key0) {
+    uint8_t f = 0;
+    if (hash && epoch && key0) {       // enumerate_matches (splinter.c:982) + _search.c:366,375
+        f |= SPL_ROW_ENUM;
+        if (val_len > 0) f |= SPL_ROW_LIST;  // splinter_list (splinter.c:470-471)
+    }
+    return f;
+}
+
+static bool row_is_zero(const uint8_t *p, size_t bytes) {
+    const uint64_t *w = reinterpret_cast<const uint64_t *>(p);
+    uint64_t acc = 0;
+    for (size_t i = 0; i < bytes / 8; i++) acc |= w[i];
+    return acc == 0;
+}
+
+static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, bool header_moved, SyncCounters *scp) {
+    using namespace layout;
+    SyncCounters &sc = *scp;
+    cudaSetDevice(c->device);
+    StageBuf *rb = &c->stage[(size_t)tid * 4], *mb = &c->stage[(size_t)tid * 4 + 2];
+    int rcur = 0, mcur = 0;
+    if (acquire_buf(rb[0]) || acquire_buf(mb[0])) { sc.err = 1; return; }
+    const size_t row_bytes = (size_t)c->dim * 4;
+    for (uint64_t r = lo; r < hi; r++) {
+        const uint8_t *sl = c->base + kHeaderSize + (c->slot_begin + r) * c->slot_size;
+        const uint64_t h = ld_acq64(sl + S_HASH);
+        const uint64_t e1 = ld_acq64(sl + S_EPOCH);
+        const uint8_t st = c->c_state[r];
+        bool row_dirty = !(st & 1) || h != c->c_hash[r] || e1 != c->c_epoch[r];
+        if (!(st & 1) && h == 0 && e1 == 0) {
+            // never-used slot on a never-mirrored row: the zero-initialised mirror is already right
+            c->c_state[r] = 1;
+            continue;
+        }
+        if (!row_dirty && header_moved && e1 == 4 && (st & 2)) {
+            // retrain ABA (splinter.c:807-825): the epoch is forced to 4, which is also where a
+            // set + set_embedding slot naturally sits.  A scrubbed row is all-zero: probe it.
+            const uint64_t probe0 = *reinterpret_cast<const uint64_t *>(sl + S_EMBED);
+            if (probe0 == 0 && row_is_zero(sl + S_EMBED, row_bytes)) { row_dirty = true; sc.aba++; }
+        }
+        if (!row_dirty) {
+            // label changes move no slot epoch (splinter.c:843): compare bloom + validity bits
+            const uint64_t b = ld_acq64(sl + S_BLOOM);
+            const uint8_t f = validity_bits(h, e1, ld_acq32(sl + S_VAL_LEN), sl[S_KEY]) | (c->c_flags[r] & SPL_ROW_EMB);
+            if (b != c->c_bloom[r] || f != c->c_flags[r]) {
+                StageBuf &m = mb[mcur];
+                m.h_meta[m.n++] = StagedMeta{ b, e1, (uint32_t)r, f };
+                c->c_bloom[r] = b; c->c_flags[r] = f;
+                sc.meta++;
+                if (m.n == m.cap) {
+                    if (flush_buf(c, m, false, sc)) { sc.err = 1; return; }
+                    mcur ^= 1;
+                    if (acquire_buf(mb[mcur])) { sc.err = 1; return; }
+                }
+            }
+            continue;
+        }
+        // ---- seqlock-validated row copy ----
+        StageBuf &b = rb[rcur];
+        float *dst = b.h_rows + (size_t)b.n * c->dim;
+        bool ok = false;
+        uint64_t es = e1, hh = h, bloom = 0;
+        uint32_t vl = 0; uint8_t key0 = 0;
+        for (int attempt = 0; attempt < 4 && !ok; attempt++) {
+            if (attempt) { es = ld_acq64(sl + S_EPOCH); }
+            if (es & 1) continue;                       // writer active: splinter.c:599 returns EAGAIN
+            memcpy(dst, sl + S_EMBED, row_bytes);
+            hh = ld_acq64(sl + S_HASH);
+            bloom = ld_acq64(sl + S_BLOOM);
+            vl = ld_acq32(sl + S_VAL_LEN);
+            key0 = sl[S_KEY];
+            std::atomic_thread_fence(std::memory_order_acquire);
+            ok = ld_acq64(sl + S_EPOCH) == es;          // splinter.c:602-603
+        }
+        if (!ok) {
+            sc.busy++;
+            if (!(st & 1)) {
+                // never mirrored and busy right now: publish validity without an embedding so the
+                // slot scores like a failed splinter_get_embedding (_search.c:388-391)
+                const uint8_t f = validity_bits(h, e1 | 1, ld_acq32(sl + S_VAL_LEN), sl[S_KEY]);
+                StageBuf &m = mb[mcur];
+                m.h_meta[m.n++] = StagedMeta{ ld_acq64(sl + S_BLOOM), es, (uint32_t)r, f };
+                if (m.n == m.cap) {
+                    if (flush_buf(c, m, false, sc)) { sc.err = 1; return; }
+                    mcur ^= 1;
+                    if (acquire_buf(mb[mcur])) { sc.err = 1; return; }
+                }
+            }
+            continue;  // keep the previous mirror row and the previous cache: retried next sync
+        }
+        const uint8_t f = validity_bits(hh, es, vl, key0) | SPL_ROW_EMB;
+        b.h_meta[b.n] = StagedMeta{ bloom, es, (uint32_t)r, f };
+        b.n++;
+        c->c_hash[r] = hh; c->c_epoch[r] = es; c->c_bloom[r] = bloom; c->c_flags[r] = f;
+        c->c_state[r] = 1 | (row_is_zero(reinterpret_cast<const uint8_t *>(dst), row_bytes) ? 0 : 2);
+        sc.rows++;
+        if (b.n == b.cap) {
+            if (flush_buf(c, b, true, sc)) { sc.err = 1; return; }
+            rcur ^= 1;
+            if (acquire_buf(rb[rcur])) { sc.err = 1; return; }
+        }
+    }
+    if (flush_buf(c, rb[rcur], true, sc) || flush_buf(c, mb[mcur], false, sc)) sc.err = 1;
+}
+
+extern "C" int spl_gpu_sync(spl_gpu_ctx *c, spl_gpu_sync_stats *stats) {
+    if (!c) return fail(-2, EINVAL, "null context");
+    if (c->dense) return fail(-2, EINVAL, "dense contexts have no backing store to sync");
+    static std::mutex sync_mu;  // one sweep at a time per process keeps the host caches single-writer
+    std::lock_guard<std::mutex> sweep_lock(sync_mu);
+    auto t0 = std::chrono::steady_clock::now();
+    const uint64_t hdr_epoch = ld_acq64(c->base + layout::H_EPOCH);
+    const bool header_moved = c->first_sync || hdr_epoch != c->c_header_epoch;
+    SyncCounters sc;
+    const unsigned T = c->sync_threads;
+    std::vector<std::thread> th;
+    const uint64_t per = (c->n + T - 1) / T;
+    for (unsigned t = 0; t < T; t++) {
+        uint64_t lo = per * t, hi = lo + per;
+        if (lo > c->n) lo = c->n;
+        if (hi > c->n) hi = c->n;
+        th.emplace_back(sync_worker, c, t, lo, hi, header_moved, &sc);
+    }
+    for (auto &x : th) x.join();
+    auto t1 = std::chrono::steady_clock::now();
+    if (sc.err.load()) return fail(-1, EIO, "sync worker failed while staging rows to the device");
+    cudaSetDevice(c->device);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    for (StageBuf &b : c->stage) b.in_flight = false;
+    auto t2 = std::chrono::steady_clock::now();
+    c->c_header_epoch = hdr_epoch;
+    c->first_sync = false;
+    const uint64_t gen = ++c->generation;
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        stats->generation = gen;
+        stats->slots_swept = c->n;
+        stats->rows_uploaded = sc.rows;
+        stats->meta_updated = sc.meta;
+        stats->skipped_busy = sc.busy;
+        stats->aba_rechecked = sc.aba;
+        stats->bytes_h2d = sc.bytes;
+        stats->sweep_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        stats->upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
+        stats->header_epoch = hdr_epoch;
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// dense shards
+// ------------------------------------------------------------------------------------------------
+extern "C" int spl_gpu_dense_upload(spl_gpu_ctx *c, uint64_t first_row, uint64_t n_rows, const float *E,
+                                    const uint64_t *bloom, const uint8_t *flags, const uint64_t *epoch) {
+    if (!c || !E) return fail(-2, EINVAL, "null argument");
+    if (!c->dense) return fail(-2, EINVAL, "store-backed contexts are filled by spl_gpu_sync");
+    if (first_row + n_rows > c->n) return fail(-2, EINVAL, "row range beyond the shard");
+    cudaSetDevice(c->device);
+    SyncCounters sc;
+    StageBuf *rb = &c->stage[0];
+    int cur = 0;
+    if (acquire_buf(rb[0])) return -1;
+    const size_t row_bytes = (size_t)c->dim * 4;
+    for (uint64_t r = 0; r < n_rows; r++) {
+        StageBuf &b = rb[cur];
+        memcpy(b.h_rows + (size_t)b.n * c->dim, E + r * c->dim, row_bytes);
+        b.h_meta[b.n] = StagedMeta{ bloom ? bloom[r] : 0, epoch ? epoch[r] : 2, (uint32_t)(first_row + r),
+                                    flags ? flags[r] : (uint32_t)(SPL_ROW_LIST | SPL_ROW_ENUM | SPL_ROW_EMB) };
+        if (++b.n == b.cap) {
+            if (flush_buf(c, b, true, sc)) return -1;
+            cur ^= 1;
+            if (acquire_buf(rb[cur])) return -1;
+        }
+    }
+    if (flush_buf(c, rb[cur], true, sc)) return -1;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    rb[0].in_flight = rb[1].in_flight = false;
+    ++c->generation;
+    return 0;
+}
+
+extern "C" int spl_gpu_dense_fill_synthetic(spl_gpu_ctx *c, uint64_t seed_corpus, uint64_t seed_bloom) {
+    if (!c) return fail(-2, EINVAL, "null context");
+    if (!c->dense) return fail(-2, EINVAL, "only dense contexts can be filled synthetically");
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->d_synth_scale) {
+        int rc = dev_alloc(c, &c->d_synth_scale, c->n, false);
+        if (rc) return rc;
+    }
+    CUDA_TRY(launch_synth(c->m, c->n, c->slot_begin, seed_corpus, seed_bloom, c->d_synth_scale, c->sm_count, c->stream));
+    c->launches += 2;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    ++c->generation;
+    return 0;
+}
+
+extern "C" int spl_gpu_read_mirror(spl_gpu_ctx *c, uint64_t first_slot, uint64_t n, float *E, uint64_t *bloom,
+                                   uint8_t *flags, uint64_t *epoch) {
+    if (!c) return fail(-2, EINVAL, "null context");
+    if (first_slot < c->slot_begin || first_slot + n > c->slot_begin + c->n) return fail(-2, EINVAL, "range outside the shard");
+    const uint64_t r0 = first_slot - c->slot_begin;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    if (E) CUDA_TRY(cudaMemcpy(E, c->m.E + r0 * c->dim, n * c->dim * 4, cudaMemcpyDeviceToHost));
+    if (bloom) CUDA_TRY(cudaMemcpy(bloom, c->m.bloom + r0, n * 8, cudaMemcpyDeviceToHost));
+    if (flags) CUDA_TRY(cudaMemcpy(flags, c->m.flags + r0, n, cudaMemcpyDeviceToHost));
+    if (epoch) CUDA_TRY(cudaMemcpy(epoch, c->m.epoch + r0, n * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// search
+// ------------------------------------------------------------------------------------------------
+static int check_params(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {
+    if (!c || !p) return fail(-2, EINVAL, "null argument");
+    if (p->struct_size != sizeof(spl_gpu_search_params)) return fail(-2, EINVAL, "spl_gpu_search_params size mismatch");
+    if (p->dim != c->dim) return fail(-2, EINVAL, "query dim %u != mirror dim %u", p->dim, c->dim);
+    if (p->nq == 0 || p->nq > kMaxBatchQ) return fail(-2, EINVAL, "nq must be in 1..%u", kMaxBatchQ);
+    if (p->order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order %u", p->order);
+    if (p->mode > SPL_MODE_BATCH_BF16) return fail(-2, EINVAL, "unknown mode %u", p->mode);
+    return 0;
+}
+
+static void fill_args(const spl_gpu_ctx *c, const spl_gpu_search_params *p, ScanArgs &a) {
+    memset(&a, 0, sizeof a);
+    a.E = c->m.E; a.bloom = c->m.bloom; a.flags = c->m.flags; a.epoch = c->m.epoch;
+    a.n = (uint32_t)c->n; a.dim = c->dim; a.k = p->k; a.order = p->order;
+    a.mask = p->bloom_mask; a.min_sim = p->min_similarity; a.max_dist = p->max_distance;
+    a.exclude = kIdxSentinel;
+    if (p->exclude_slot != SPL_NO_SLOT && p->exclude_slot >= c->slot_begin && p->exclude_slot < c->slot_begin + c->n)
+        a.exclude = (uint32_t)(p->exclude_slot - c->slot_begin);
+    a.row0 = c->slot_begin;
+    a.cta_cands = c->d_cands; a.counters = c->d_counters;
+}
+
+// enqueue one fused top-k scan per query (k in 1..KMAX_FUSED); caller holds c->mu
+static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, spl_gpu_result *d_out,
+                         uint32_t out_stride, uint32_t *d_counts, cudaStream_t s) {
+    uint32_t mode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
+    if (mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "mode %u is not available for this query shape", mode);
+    ScanArgs a;
+    fill_args(c, p, a);
+    for (uint32_t qi = 0; qi < p->nq; qi++) {
+        a.q = d_q + (size_t)qi * c->dim;
+        a.out = d_out + (size_t)qi * out_stride;
+        a.out_count = d_counts + qi;
+        CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
+        c->launches++;
+    }
+    return 0;
+}
+
+extern "C" int spl_gpu_search_device(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q,
+                                     spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, void *stream) {
+    int rc = check_params(c, p);
+    if (rc) return rc;
+    if (!d_q || !d_out || !d_counts) return fail(-2, EINVAL, "null device buffer");
+    if (p->k == 0 || p->k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "device search needs k in 1..%u", SPL_GPU_KMAX_FUSED);
+    if (out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    return enqueue_fused(c, p, d_q, d_out, out_stride, d_counts, stream ? (cudaStream_t)stream : c->stream);
+}
+
+static int ensure_sort_scratch(spl_gpu_ctx *c, uint32_t out_cap) {
+    int rc;
+    if (!c->d_keys) {
+        if ((rc = dev_alloc(c, &c->d_keys, c->n, false))) return rc;
+        c->sort_tmp_bytes = sortall_tmp_bytes((uint32_t)c->n);
+        unsigned char *tmp = nullptr;
+        if ((rc = dev_alloc(c, &tmp, c->sort_tmp_bytes, false))) return rc;
+        c->d_sort_tmp = tmp;
+    }
+    if (c->big_out_cap < out_cap) {
+        if (c->d_big_out) { cudaFree(c->d_big_out); c->d_big_out = nullptr; }
+        if ((rc = dev_alloc(c, &c->d_big_out, out_cap, false))) return rc;
+        c->big_out_cap = out_cap;
+    }
+    return 0;
+}
+
+extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
+                              uint32_t out_stride, uint32_t *counts) {
+    int rc = check_params(c, p);
+    if (rc) return rc;
+    if (!q || !out || !counts) return fail(-2, EINVAL, "null buffer");
+    if (p->k > 0 && out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
+    if (p->k == 0 && out_stride == 0) return fail(-2, EINVAL, "out_stride must be > 0");
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    const size_t qbytes = (size_t)c->dim * sizeof(float);
+    const bool fused = p->k >= 1 && p->k <= SPL_GPU_KMAX_FUSED;
+    if (fused) {
+        // process in chunks of q_cap queries through the pinned staging buffers
+        for (uint32_t q0 = 0; q0 < p->nq; q0 += c->q_cap) {
+            const uint32_t nq = (p->nq - q0 < c->q_cap) ? p->nq - q0 : c->q_cap;
+            spl_gpu_search_params pp = *p;
+            pp.nq = nq;
+            memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
+            CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
+            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+            if ((rc = enqueue_fused(c, &pp, c->d_q, c->d_out, p->k, c->d_count, c->stream))) return rc;
+            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+            CUDA_TRY(cudaMemcpyAsync(c->h_out, c->d_out, (size_t)nq * p->k * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(cudaMemcpyAsync(c->h_count, c->d_count, nq * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            if (c->timing) {
+                float ms = 0.f;
+                CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+                c->last_scan_ms = ms / nq;
+            }
+            for (uint32_t i = 0; i < nq; i++) {
+                counts[q0 + i] = c->h_count[i];
+                memcpy(out + (size_t)(q0 + i) * out_stride, c->h_out + (size_t)i * p->k, (size_t)c->h_count[i] * sizeof(spl_gpu_result));
+            }
+        }
+        return 0;
+    }
+    // ---- unlimited / large k: key-per-row scan + device-wide sort (cold path) ----
+    uint32_t mode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
+    if (mode != SPL_MODE_FAST && mode != SPL_MODE_EXACT) return fail(-1, ENOSYS, "mode %u cannot serve k = %u", mode, p->k);
+    const uint32_t want = p->k == 0 ? out_stride : p->k;
+    const uint32_t cap = want < c->n ? want : (uint32_t)c->n;
+    if ((rc = ensure_sort_scratch(c, cap))) return rc;
+    ScanArgs a;
+    fill_args(c, p, a);
+    for (uint32_t qi = 0; qi < p->nq; qi++) {
+        memcpy(c->h_q, q + (size_t)qi * c->dim, qbytes);
+        CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, qbytes, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaMemsetAsync(c->d_keys, 0xFF, c->n * sizeof(uint64_t), c->stream));
+        a.q = c->d_q;
+        a.keys_out = c->d_keys;
+        a.out = c->d_big_out;
+        a.out_count = c->d_count;
+        a.k = 0;
+        CUDA_TRY(launch_scan_fast(a, c->scan_grid, c->stream));
+        CUDA_TRY(launch_sortall(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, cap, c->stream));
+        c->launches += 4;
+        CUDA_TRY(cudaMemcpyAsync(c->h_count, c->d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        const uint32_t total = c->h_count[0];
+        const uint32_t ncopy = total < cap ? total : cap;
+        CUDA_TRY(cudaMemcpy(out + (size_t)qi * out_stride, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost));
+        counts[qi] = p->k == 0 ? total : ncopy;
+    }
+    return 0;
+}
+
+extern "C" int spl_gpu_merge_topk_device(spl_gpu_ctx *c, const spl_gpu_result *d_lists, const uint32_t *d_counts,
+                                         uint32_t nlists, uint32_t list_stride, uint32_t order, uint32_t k,
+                                         spl_gpu_result *d_out, uint32_t *d_out_count, void *stream) {
+    if (!c || !d_lists || !d_counts || !d_out || !d_out_count) return fail(-2, EINVAL, "null argument");
+    if (k == 0 || k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "merge needs k in 1..%u", SPL_GPU_KMAX_FUSED);
+    if (order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order");
+    cudaSetDevice(c->device);
+    CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, list_stride, order, k, d_out, d_out_count,
+                                  stream ? (cudaStream_t)stream : c->stream));
+    c->launches++;
+    return 0;
+}

@@ -1,0 +1,393 @@
+// spl_scan.cu -- single-query fused scan (SPL_MODE_FAST) for sm_100a.
+//
+// One launch does, per query, everything the reference's cmd_search does after it has its
+// query vector (/root/reference/splinter_cli_cmd_search.c:336-416):
+//   candidate predicate   splinter_enumerate_matches (splinter.c:977-989) / splinter_list
+//                         (splinter.c:466-477) + the epoch!=0 / key / scratch-key skips
+//                         (_search.c:365-375), evaluated from 9 bytes per slot (bloom u64 +
+//                         flags u8) BEFORE any embedding byte of the slot is requested;
+//   scoring               cosine_similarity + euclidean_distance (_search.c:43-62) fused in one
+//                         pass over the row: dot, |e|^2 and sum (q-e)^2 from 128-bit coalesced
+//                         streaming loads, per-lane partial sums, warp-shuffle tree;
+//   thresholds            --similarity / --distance (_search.c:398-399);
+//   sort + limit          compare_results + qsort + limit (_search.c:64-72,412-416) as a
+//                         per-warp bounded list -> per-CTA list -> last-CTA merge + sort.
+//
+// HBM-bound by design: algorithmic bytes per query = 9*n + 4*dim*M (M = rows passing the
+// predicate) + 4*dim.  Rows are handed out dynamically in groups of 32 slots so a selective
+// mask does not unbalance the warps.
+#include "spl_scan.cuh"
+
+#include <float.h>
+
+namespace spl {
+
+// ---------------------------------------------------------------------------------------------
+// CTA epilogue shared by all single-query scan kernels: fold the kScanWarps per-warp lists into
+// one list per CTA, publish it, and let the last CTA to finish merge all CTAs' lists, sort the
+// survivors and write the result records.  Also re-arms the scratch counters for the next launch.
+// ---------------------------------------------------------------------------------------------
+__device__ void scan_epilogue(const ScanArgs &a, WarpTopK &W, uint64_t *skeys, uint32_t *sidx,
+                              uint32_t *s_flag) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t k = a.k;
+    __shared__ uint32_t s_cnt[kScanWarps];
+    if (lane == 0) s_cnt[warp] = W.cnt;
+    __syncthreads();
+    if (warp == 0) {
+        for (uint32_t w = 1; w < kScanWarps; w++) W.absorb(skeys + w * k, sidx + w * k, s_cnt[w], lane);
+        Cand *dst = a.cta_cands + (size_t)blockIdx.x * k;
+        for (uint32_t p = lane; p < k; p += kWarp) {
+            Cand c;
+            c.key = p < W.cnt ? W.keys[p] : kKeySentinel;
+            c.idx = p < W.cnt ? W.idxs[p] : kIdxSentinel;
+            c.pad = 0;
+            dst[p] = c;
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+            uint32_t ticket = atomicAdd(&a.counters[1], 1u);
+            *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
+        }
+    }
+    __syncthreads();
+    if (*s_flag == 0) return;
+
+    // ---- last CTA: merge gridDim.x lists of k ----
+    __threadfence();
+    W.init(skeys + warp * k, sidx + warp * k, k);
+    for (uint32_t c = warp; c < gridDim.x; c += kScanWarps) W.absorb(a.cta_cands + (size_t)c * k, k, lane);
+    if (lane == 0) s_cnt[warp] = W.cnt;
+    __syncthreads();
+    if (warp == 0) {
+        for (uint32_t w = 1; w < kScanWarps; w++) W.absorb(skeys + w * k, sidx + w * k, s_cnt[w], lane);
+        if (lane == 0) { s_cnt[0] = W.cnt; a.counters[0] = 0; a.counters[1] = 0; *a.out_count = W.cnt; }
+    }
+    __syncthreads();
+    // rank sort: entry t goes to position (#entries that beat it); k <= blockDim.x * iterations
+    const uint32_t cnt = s_cnt[0];
+    for (uint32_t t = threadIdx.x; t < cnt; t += blockDim.x) {
+        const uint64_t key = skeys[t];
+        const uint32_t idx = sidx[t];
+        uint32_t rank = 0;
+        for (uint32_t j = 0; j < cnt; j++) rank += better(skeys[j], sidx[j], key, idx) ? 1u : 0u;
+        spl_gpu_result r;
+        split_key(a.order, key, r.similarity, r.distance);
+        r.slot_idx = (uint32_t)(a.row0 + idx);
+        r.has_embedding = (a.flags[idx] & SPL_ROW_EMB) ? 1u : 0u;
+        r.epoch = a.epoch[idx];
+        r.bloom = a.bloom[idx];
+        a.out[rank] = r;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// SPL_MODE_FAST: one warp per row, V float4 per lane (dim = 128*V), two rows in flight.
+// ---------------------------------------------------------------------------------------------
+template <int V, bool KEYS>
+__global__ void __launch_bounds__(kScanThreads, 3) scan_fast_kernel(const ScanArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_flag;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
+    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + (size_t)kScanWarps * a.k);
+    WarpTopK W;
+    W.init(skeys + warp * a.k, sidx + warp * a.k, a.k);
+
+    // query -> registers; |q|^2 once per warp
+    const float4 *q4 = reinterpret_cast<const float4 *>(a.q);
+    float4 qv[V];
+    float ma = 0.f;
+#pragma unroll
+    for (int j = 0; j < V; j++) {
+        qv[j] = q4[j * 32 + lane];
+        ma = fmaf(qv[j].x, qv[j].x, ma); ma = fmaf(qv[j].y, qv[j].y, ma);
+        ma = fmaf(qv[j].z, qv[j].z, ma); ma = fmaf(qv[j].w, qv[j].w, ma);
+    }
+    ma = warp_sum(ma);
+
+    const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+    const uint32_t ngroups = (a.n + 31u) >> 5;
+    const float4 *E4 = reinterpret_cast<const float4 *>(a.E);
+    const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+
+    auto fetch_group = [&]() -> uint32_t {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(&a.counters[0], 1u);
+        return __shfl_sync(0xffffffffu, g, 0);
+    };
+    auto load_pred = [&](uint32_t g, uint32_t &f, uint64_t &b) {
+        const uint32_t row = (g << 5) + lane;
+        f = 0; b = 0;
+        if (g < ngroups && row < a.n) { f = a.flags[row]; b = a.bloom[row]; }
+    };
+    auto finish_row = [&](uint32_t row, uint32_t f, float dot, float mb, float ss) {
+        float sim, dist;
+        if (f & SPL_ROW_EMB) {
+            sim = cosine_from_sums(dot, ma, mb);
+            dist = __fsqrt_rn(ss);
+            if (a.min_sim > 0.f && sim < a.min_sim) return;
+            if (a.max_dist > 0.f && dist > a.max_dist) return;
+        } else {  // _search.c:388-393
+            if (thresholds) return;
+            sim = 0.f; dist = FLT_MAX;
+        }
+        const uint64_t key = make_key(a.order, sim, dist);
+        if (KEYS) {  // unlimited / large-k path: publish the key, a device-wide sort follows
+            if (lane == 0) a.keys_out[row] = key;
+        } else if (W.admits(key, row)) {
+            W.insert(key, row, lane);
+        }
+    };
+
+    uint32_t g = fetch_group(), f; uint64_t b;
+    load_pred(g, f, b);
+    while (g < ngroups) {
+        const uint32_t gn = fetch_group();
+        const uint32_t row_l = (g << 5) + lane;
+        const bool pass = (f & need) && ((b & a.mask) == a.mask) && row_l != a.exclude;
+        unsigned m = __ballot_sync(0xffffffffu, pass);
+        uint32_t fn; uint64_t bn;
+        bool prefetched = false;
+        if (m == 0) { load_pred(gn, fn, bn); prefetched = true; }
+        while (m) {
+            const int l0 = __ffs(m) - 1; m &= m - 1;
+            const bool two = m != 0;
+            const int l1 = two ? __ffs(m) - 1 : l0;
+            if (two) m &= m - 1;
+            const uint32_t r0 = (g << 5) + l0, r1 = (g << 5) + l1;
+            const float4 *p0 = E4 + (size_t)r0 * (V * 32) + lane;
+            const float4 *p1 = E4 + (size_t)r1 * (V * 32) + lane;
+            float4 x[V], y[V];
+#pragma unroll
+            for (int j = 0; j < V; j++) x[j] = ldg_stream(p0 + 32 * j);
+            if (two) {
+#pragma unroll
+                for (int j = 0; j < V; j++) y[j] = ldg_stream(p1 + 32 * j);
+            }
+            // the next group's predicate bytes ride behind the first row loads of this group
+            if (!prefetched) { load_pred(gn, fn, bn); prefetched = true; }
+            float d0 = 0.f, b0 = 0.f, s0 = 0.f, d1 = 0.f, b1 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < V; j++) {
+                float t;
+                d0 = fmaf(qv[j].x, x[j].x, d0); b0 = fmaf(x[j].x, x[j].x, b0); t = qv[j].x - x[j].x; s0 = fmaf(t, t, s0);
+                d0 = fmaf(qv[j].y, x[j].y, d0); b0 = fmaf(x[j].y, x[j].y, b0); t = qv[j].y - x[j].y; s0 = fmaf(t, t, s0);
+                d0 = fmaf(qv[j].z, x[j].z, d0); b0 = fmaf(x[j].z, x[j].z, b0); t = qv[j].z - x[j].z; s0 = fmaf(t, t, s0);
+                d0 = fmaf(qv[j].w, x[j].w, d0); b0 = fmaf(x[j].w, x[j].w, b0); t = qv[j].w - x[j].w; s0 = fmaf(t, t, s0);
+            }
+            if (two) {
+#pragma unroll
+                for (int j = 0; j < V; j++) {
+                    float t;
+                    d1 = fmaf(qv[j].x, y[j].x, d1); b1 = fmaf(y[j].x, y[j].x, b1); t = qv[j].x - y[j].x; s1 = fmaf(t, t, s1);
+                    d1 = fmaf(qv[j].y, y[j].y, d1); b1 = fmaf(y[j].y, y[j].y, b1); t = qv[j].y - y[j].y; s1 = fmaf(t, t, s1);
+                    d1 = fmaf(qv[j].z, y[j].z, d1); b1 = fmaf(y[j].z, y[j].z, b1); t = qv[j].z - y[j].z; s1 = fmaf(t, t, s1);
+                    d1 = fmaf(qv[j].w, y[j].w, d1); b1 = fmaf(y[j].w, y[j].w, b1); t = qv[j].w - y[j].w; s1 = fmaf(t, t, s1);
+                }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                d0 += __shfl_xor_sync(0xffffffffu, d0, off);
+                b0 += __shfl_xor_sync(0xffffffffu, b0, off);
+                s0 += __shfl_xor_sync(0xffffffffu, s0, off);
+                d1 += __shfl_xor_sync(0xffffffffu, d1, off);
+                b1 += __shfl_xor_sync(0xffffffffu, b1, off);
+                s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+            }
+            const uint32_t f0 = __shfl_sync(0xffffffffu, f, l0), f1 = __shfl_sync(0xffffffffu, f, l1);
+            finish_row(r0, f0, d0, b0, s0);
+            if (two) finish_row(r1, f1, d1, b1, s1);
+        }
+        g = gn; f = fn; b = bn;
+    }
+    if (KEYS) {
+        // re-arm the work counter once every CTA has drained it
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) { a.counters[0] = 0; a.counters[1] = 0; }
+        }
+        return;
+    }
+    scan_epilogue(a, W, skeys, sidx, &s_flag);
+}
+
+// generic dimension (dim % 4 == 0): query in shared memory, strided float4 loop, one row at a time
+template <bool KEYS>
+__global__ void __launch_bounds__(kScanThreads, 3) scan_fast_generic_kernel(const ScanArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_flag;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
+    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + (size_t)kScanWarps * a.k);
+    float4 *sq = reinterpret_cast<float4 *>(smem_raw + ((scan_topk_smem(a.k) + 15) & ~(size_t)15));
+    WarpTopK W;
+    W.init(skeys + warp * a.k, sidx + warp * a.k, a.k);
+    const uint32_t nv = a.dim >> 2;
+    for (uint32_t c = threadIdx.x; c < nv; c += blockDim.x) sq[c] = reinterpret_cast<const float4 *>(a.q)[c];
+    __syncthreads();
+    float ma = 0.f;
+    for (uint32_t c = lane; c < nv; c += 32) {
+        float4 v = sq[c];
+        ma = fmaf(v.x, v.x, ma); ma = fmaf(v.y, v.y, ma); ma = fmaf(v.z, v.z, ma); ma = fmaf(v.w, v.w, ma);
+    }
+    ma = warp_sum(ma);
+    const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+    const uint32_t ngroups = (a.n + 31u) >> 5;
+    const float4 *E4 = reinterpret_cast<const float4 *>(a.E);
+    const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(&a.counters[0], 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        const uint32_t row_l = (g << 5) + lane;
+        uint32_t f = 0; uint64_t b = 0;
+        if (row_l < a.n) { f = a.flags[row_l]; b = a.bloom[row_l]; }
+        const bool pass = (f & need) && ((b & a.mask) == a.mask) && row_l != a.exclude;
+        unsigned m = __ballot_sync(0xffffffffu, pass);
+        while (m) {
+            const int l0 = __ffs(m) - 1; m &= m - 1;
+            const uint32_t r0 = (g << 5) + l0;
+            const float4 *p0 = E4 + (size_t)r0 * nv;
+            float d0 = 0.f, b0 = 0.f, s0 = 0.f;
+            for (uint32_t c = lane; c < nv; c += 32) {
+                const float4 x = ldg_stream(p0 + c), qq = sq[c];
+                float t;
+                d0 = fmaf(qq.x, x.x, d0); b0 = fmaf(x.x, x.x, b0); t = qq.x - x.x; s0 = fmaf(t, t, s0);
+                d0 = fmaf(qq.y, x.y, d0); b0 = fmaf(x.y, x.y, b0); t = qq.y - x.y; s0 = fmaf(t, t, s0);
+                d0 = fmaf(qq.z, x.z, d0); b0 = fmaf(x.z, x.z, b0); t = qq.z - x.z; s0 = fmaf(t, t, s0);
+                d0 = fmaf(qq.w, x.w, d0); b0 = fmaf(x.w, x.w, b0); t = qq.w - x.w; s0 = fmaf(t, t, s0);
+            }
+            d0 = warp_sum(d0); b0 = warp_sum(b0); s0 = warp_sum(s0);
+            const uint32_t f0 = __shfl_sync(0xffffffffu, f, l0);
+            float sim, dist;
+            bool keep = true;
+            if (f0 & SPL_ROW_EMB) {
+                sim = cosine_from_sums(d0, ma, b0);
+                dist = __fsqrt_rn(s0);
+                if (a.min_sim > 0.f && sim < a.min_sim) keep = false;
+                if (a.max_dist > 0.f && dist > a.max_dist) keep = false;
+            } else {
+                keep = !thresholds; sim = 0.f; dist = FLT_MAX;
+            }
+            if (keep) {
+                const uint64_t key = make_key(a.order, sim, dist);
+                if (KEYS) {
+                    if (lane == 0) a.keys_out[r0] = key;
+                } else if (W.admits(key, r0)) {
+                    W.insert(key, r0, lane);
+                }
+            }
+        }
+    }
+    if (KEYS) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) { a.counters[0] = 0; a.counters[1] = 0; }
+        }
+        return;
+    }
+    scan_epilogue(a, W, skeys, sidx, &s_flag);
+}
+
+int scan_fast_ctas_per_sm(uint32_t, uint32_t) { return 3; }
+
+template <bool KEYS>
+static cudaError_t launch_scan_fast_t(const ScanArgs &a, int grid, cudaStream_t stream) {
+    const size_t smem = KEYS ? 0 : scan_topk_smem(a.k);
+    if (a.dim == 768) {
+        scan_fast_kernel<6, KEYS><<<grid, kScanThreads, smem, stream>>>(a);
+    } else if (a.dim == 1024) {
+        scan_fast_kernel<8, KEYS><<<grid, kScanThreads, smem, stream>>>(a);
+    } else if (a.dim == 512) {
+        scan_fast_kernel<4, KEYS><<<grid, kScanThreads, smem, stream>>>(a);
+    } else if (a.dim == 256) {
+        scan_fast_kernel<2, KEYS><<<grid, kScanThreads, smem, stream>>>(a);
+    } else if (a.dim == 128) {
+        scan_fast_kernel<1, KEYS><<<grid, kScanThreads, smem, stream>>>(a);
+    } else {
+        const size_t smem_g = ((smem + 15) & ~(size_t)15) + (size_t)a.dim * 4;
+        scan_fast_generic_kernel<KEYS><<<grid, kScanThreads, smem_g, stream>>>(a);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scan_fast(const ScanArgs &a, int grid, cudaStream_t stream) {
+    return a.keys_out ? launch_scan_fast_t<true>(a, grid, stream) : launch_scan_fast_t<false>(a, grid, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// merge of result-record lists (after the per-GPU all-gather): one CTA
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kScanThreads, 1)
+merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t stride,
+                     uint32_t order, uint32_t k, spl_gpu_result *out, uint32_t *out_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_cnt[kScanWarps];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
+    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + (size_t)kScanWarps * k);
+    // the payload index carried through the lists is the flat record position l*stride+i; ties are
+    // broken by the record's global slot index, which is what `better` must see, so we carry the
+    // slot index in idx and find the record again by (key, slot) afterwards.
+    WarpTopK W;
+    W.init(skeys + warp * k, sidx + warp * k, k);
+    for (uint32_t l = warp; l < nlists; l += kScanWarps) {
+        const uint32_t n = min(counts[l], stride);
+        for (uint32_t base = 0; base < n; base += kWarp) {
+            const uint32_t p = base + lane;
+            uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
+            if (p < n) {
+                const spl_gpu_result r = lists[(size_t)l * stride + p];
+                key = make_key(order, r.similarity, r.distance);
+                idx = r.slot_idx;
+            }
+            unsigned m = __ballot_sync(0xffffffffu, idx != kIdxSentinel && W.admits(key, idx));
+            while (m) {
+                const int s = __ffs(m) - 1; m &= m - 1;
+                W.insert(__shfl_sync(0xffffffffu, key, s), __shfl_sync(0xffffffffu, idx, s), lane);
+            }
+        }
+    }
+    if (lane == 0) s_cnt[warp] = W.cnt;
+    __syncthreads();
+    if (warp == 0) {
+        for (uint32_t w = 1; w < kScanWarps; w++) W.absorb(skeys + w * k, sidx + w * k, s_cnt[w], lane);
+        if (lane == 0) { s_cnt[0] = W.cnt; *out_count = W.cnt; }
+    }
+    __syncthreads();
+    const uint32_t cnt = s_cnt[0];
+    // rank + recover the full record (epoch, bloom, has_embedding) from the source lists
+    for (uint32_t t = threadIdx.x; t < cnt; t += blockDim.x) {
+        const uint64_t key = skeys[t]; const uint32_t idx = sidx[t];
+        uint32_t rank = 0;
+        for (uint32_t j = 0; j < cnt; j++) rank += better(skeys[j], sidx[j], key, idx) ? 1u : 0u;
+        spl_gpu_result r;
+        r.slot_idx = idx; split_key(order, key, r.similarity, r.distance);
+        r.has_embedding = 1; r.epoch = 0; r.bloom = 0;
+        bool found = false;
+        for (uint32_t l = 0; l < nlists && !found; l++) {
+            const uint32_t n = min(counts[l], stride);
+            for (uint32_t i = 0; i < n; i++) {
+                const spl_gpu_result s = lists[(size_t)l * stride + i];
+                if (s.slot_idx == idx) { r.has_embedding = s.has_embedding; r.epoch = s.epoch; r.bloom = s.bloom;
+                                         r.similarity = s.similarity; r.distance = s.distance; found = true; break; }
+            }
+        }
+        out[rank] = r;
+    }
+}
+
+cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,
+                                 uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out,
+                                 uint32_t *out_count, cudaStream_t stream) {
+    merge_results_kernel<<<1, kScanThreads, scan_topk_smem(k), stream>>>(lists, counts, nlists, stride, order, k,
+                                                                         out, out_count);
+    return cudaGetLastError();
+}
+
+}  // namespace spl

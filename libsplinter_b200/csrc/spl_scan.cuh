@@ -1,0 +1,51 @@
+// spl_scan.cuh -- argument block shared by the single-query scan kernels and their launchers.
+#pragma once
+#include "spl_device.cuh"
+
+namespace spl {
+
+struct ScanArgs {
+    // mirror (device)
+    const float *E;          // [n][dim] fp32, row pitch = dim*4 bytes
+    const uint64_t *bloom;   // [n]
+    const uint8_t *flags;    // [n] SPL_ROW_*
+    const uint64_t *epoch;   // [n]
+    // query
+    const float *q;          // [dim]
+    uint32_t n, dim, k, order;
+    uint64_t mask;
+    float min_sim, max_dist;
+    uint32_t exclude;        // local row index to skip, kIdxSentinel = none
+    uint64_t row0;           // global slot index of local row 0
+    // scratch (device): one Cand[k] list per CTA + {work counter, done counter}
+    Cand *cta_cands;
+    uint32_t *counters;
+    // output (device)
+    spl_gpu_result *out;
+    uint32_t *out_count;
+    // unlimited / large-k path: when non-null the kernel writes one key per surviving row here
+    // (pre-filled with kKeySentinel by the caller) instead of keeping a top-k
+    uint64_t *keys_out;
+};
+
+constexpr int kScanThreads = 256;
+constexpr int kScanWarps = kScanThreads / 32;
+
+// smem bytes the fused top-k needs for a given k
+__host__ __device__ inline size_t scan_topk_smem(uint32_t k) { return (size_t)kScanWarps * k * (sizeof(uint64_t) + sizeof(uint32_t)); }
+
+cudaError_t launch_scan_fast(const ScanArgs &a, int grid, cudaStream_t stream);
+int scan_fast_ctas_per_sm(uint32_t dim, uint32_t k);
+
+// merge nlists lists of Cand-like results (spl_gpu_result records) into the top-k
+cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,
+                                 uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out,
+                                 uint32_t *out_count, cudaStream_t stream);
+
+// unlimited / k > SPL_GPU_KMAX_FUSED: sort (key, row) pairs of a whole shard and emit records.
+// keys[n] holds the scan's output; tmp buffers are caller-allocated (see sortall_tmp_bytes).
+size_t sortall_tmp_bytes(uint32_t n);
+cudaError_t launch_sortall(const ScanArgs &a, uint64_t *keys, void *tmp, size_t tmp_bytes, uint32_t out_cap,
+                           cudaStream_t stream);
+
+}  // namespace spl

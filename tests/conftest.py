@@ -1,0 +1,23 @@
+import os
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _built():
+    """Build the libraries once if they are missing (CPU container); the GPU box gets them prebuilt."""
+    from libsplinter_b200 import LIB_PATH
+    if not LIB_PATH.exists() or not (ROOT / "oracle" / "libspl_oracle.so").exists():
+        import __graft_entry__ as g
+        g.build()
+    yield
