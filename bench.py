@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the similarity-search hot path (BASELINE.json).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one query: label predicate + fused cosine/L2 scoring
++ top-k over the whole (sharded) slot mirror.
+
+  N = 1  workload C2: 2^20 slots x 768 fp32, single-query cosine top-10, bloom mask 0x3
+         (the all-matching mask and the unfiltered scan ride along as `variants`).
+  N > 1  workload C4: 2^26 slots x 768 fp32 sharded by slot range over N GPUs, single-query
+         cosine top-100, per-GPU top-k all-gathered over NCCL and merged on the device.
+
+metric = scanned GB/s, whole job (algorithmic bytes of SURVEY 8(d): 9 B per slot + 4*D per slot
+that passes the label predicate + the query), which is the BASELINE.json quantity that is
+comparable across shard sizes; queries/s is printed beside it.  `value` is measured with the
+query and the result buffers resident in HBM (CUDA events on the launching stream); `e2e` is
+the same metric through the host-buffer C-ABI call (pinned H2D of the query + D2H of the hits
+inside the timed region).  `--impl reference` times the reference's own CPU code
+(oracle/_ref: its cosine_similarity / euclidean_distance / compare_results + qsort, split
+over all host cores) on the same config.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+DIM = 768
+SEED_CORPUS, SEED_BLOOM, SEED_QUERY = 1234, 99, 4321
+C2_ROWS, C2_K, C2_MASK = 1 << 20, 10, 0x3
+C4_ROWS, C4_K = 1 << 26, 100
+N_QUERIES = 64
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6 or not f[0].isdigit():
+                continue
+            sm.append(int(f[0])); mx.append(int(f[1]))
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": int(statistics.median(sm)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(n_rows, n_pass):
+    """8 (bloom) + 1 (flags) per slot, 4*D per slot passing the predicate, + the query."""
+    return 9 * n_rows + 4 * DIM * n_pass + 4 * DIM
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    import support
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    if not support.have_ref():
+        # the reference did compile in the build container; if oracle/_ref did not travel, fall back to the port
+        kind = "port"
+    else:
+        kind = "reference"
+    cores = os.cpu_count() or 1
+    single = args.gpus == 1
+    k, mask = (C2_K, C2_MASK) if single else (C4_K, 0)
+    n = C2_ROWS  # C2 in full; for C4 a 2^20-row sample of the 2^26 (GB/s is size-independent)
+    E, bloom, flags = support.synth_dense(SEED_CORPUS, SEED_BLOOM, 0, n, DIM)
+    q = support.synth_queries(SEED_QUERY, N_QUERIES, DIM)
+    need = support.F_ENUM if mask else support.F_LIST
+    cand = (((flags & need) != 0) & ((bloom & np.uint64(mask)) == np.uint64(mask))).astype(np.uint8)
+    n_pass = int(cand.sum())
+    nbytes = algorithmic_bytes(n, n_pass)
+
+    def step(i, threads):
+        qi = q[i % N_QUERIES]
+        if kind == "reference":
+            oi, os_, od = np.zeros(k, np.uint32), np.zeros(k, np.float32), np.zeros(k, np.float32)
+            support.ref_search().ref_topk_dense(support._p(qi), support._p(E), n, DIM, support._p(cand), 0.0, 0.0, k,
+                                                threads, support._p(oi), support._p(os_), support._p(od))
+        else:
+            support.oracle_search_dense(qi, E, bloom, flags, k=k, bloom_mask=mask, threads=threads)
+
+    for i in range(args.warmup):
+        step(i, cores)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step(i, cores)
+    dt = time.perf_counter() - t0
+    gbs = nbytes * args.steps / dt / 1e9
+    qps = args.steps / dt * (n / (C2_ROWS if single else C4_ROWS))
+    sample = ("every query over the full 2^20-slot corpus" if single else
+              "2^20-slot sample of the 2^26-slot corpus; queries/s scaled by 2^20/2^26, GB/s is size-independent")
+    line = {
+        "impl": "reference", "metric": "scanned_GB_per_s", "value": round(gbs, 3), "unit": "GB/s",
+        "queries_per_s": round(qps, 4), "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": round(gbs, 3), "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": round(gbs, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(n_gpus):
+    if n_gpus == 1:
+        return {"workload": "C2: 2^20 slots x 768-d fp32, single-query cosine top-10, bloom-label pre-filter mask 0x3 "
+                            "(12.2% of slots pass); mirror resident in HBM (3.2 GB > 126 MB L2, no flush needed)",
+                "slots": C2_ROWS, "dim": DIM, "k": C2_K, "bloom_mask": "0x3", "parallelism": "1 GPU",
+                "l2_policy": "inputs larger than L2"}
+    return {"workload": f"C4: 2^26 slots x 768-d fp32 sharded by slot range over {n_gpus} GPUs, single-query cosine "
+                        "top-100, per-GPU top-k all-gathered over NCCL + device merge",
+            "slots": C4_ROWS, "dim": DIM, "k": C4_K, "bloom_mask": "0", "parallelism": f"slot-range shards x{n_gpus}",
+            "l2_policy": "inputs larger than L2"}
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def cpu_baseline_leg(k, mask, seconds=12.0):
+    """The reference's own CPU search (oracle/_ref) on the box's host cores, bounded sample."""
+    import support
+    cores = os.cpu_count() or 1
+    n = 1 << 18  # 2^18-slot sample (805 MB): generation stays in seconds; GB/s is size-independent
+    E, bloom, flags = support.synth_dense(SEED_CORPUS, SEED_BLOOM, 0, n, DIM)
+    q = support.synth_queries(SEED_QUERY, 8, DIM)
+    need = support.F_ENUM if mask else support.F_LIST
+    cand = (((flags & need) != 0) & ((bloom & np.uint64(mask)) == np.uint64(mask))).astype(np.uint8)
+    nbytes = algorithmic_bytes(n, int(cand.sum()))
+    kind = "reference" if support.have_ref() else "port"
+    out = {}
+    for label, threads in (("all_cores", cores), ("one_thread", 1)):
+        t0 = time.perf_counter()
+        steps = 0
+        while True:
+            qi = q[steps % 8]
+            if kind == "reference":
+                oi, os_, od = np.zeros(k, np.uint32), np.zeros(k, np.float32), np.zeros(k, np.float32)
+                support.ref_search().ref_topk_dense(support._p(qi), support._p(E), n, DIM, support._p(cand), 0.0, 0.0,
+                                                    k, threads, support._p(oi), support._p(os_), support._p(od))
+            else:
+                support.oracle_search_dense(qi, E, bloom, flags, k=k, bloom_mask=mask, threads=threads)
+            steps += 1
+            dt = time.perf_counter() - t0
+            if dt > seconds / 2 and steps >= 3:
+                break
+        out[label] = (nbytes * steps / dt / 1e9, steps / dt * n)
+    return {
+        "value": round(out["all_cores"][0], 3), "unit": "GB/s", "cores": cores, "kind": kind,
+        "sample": f"2^18-slot sample of the workload, ~{seconds / 2:.0f} s per leg; the reference's scorers + qsort "
+                  "split over all host cores (the shipped reference is single-threaded)",
+        "slots_per_s": round(out["all_cores"][1]),
+        "one_thread": {"value": round(out["one_thread"][0], 3), "unit": "GB/s", "slots_per_s": round(out["one_thread"][1])},
+    }
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import libsplinter_b200 as sg
+    import support
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch multi-GPU runs with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    single = world == 1
+    total_rows = C2_ROWS if single else C4_ROWS
+    k = C2_K if single else C4_K
+    rows = total_rows // world
+    row0 = rank * rows
+    peak, peak_src = measured_peaks()
+
+    m = sg.Mirror.open_dense(rows, DIM, global_row0=row0, device=local_rank)
+    m.fill_synthetic(SEED_CORPUS, SEED_BLOOM)
+    _, bloom_h, flags_h, _ = m.read_mirror(row0, rows, want_E=False)
+
+    q_host = support.synth_queries(SEED_QUERY, N_QUERIES, DIM)
+    q_dev = torch.from_numpy(q_host).to(dev)
+    out_dev = torch.zeros((k, 32), dtype=torch.uint8, device=dev)
+    cnt_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+    gathered = torch.zeros((world, k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
+    gcnt = torch.zeros(world, dtype=torch.int32, device=dev) if world > 1 else None
+    fin_dev = torch.zeros((k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
+    fcnt_dev = torch.zeros(1, dtype=torch.int32, device=dev) if world > 1 else None
+    q_pin = torch.from_numpy(q_host).pin_memory()
+    res_pin = torch.zeros((k, 32), dtype=torch.uint8).pin_memory()
+    # A dedicated (non-default) stream: the kernels, the NCCL ops and the timing events must all sit on
+    # the SAME stream -- torch.cuda.Event only sees torch's current stream.
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
+
+    def n_pass_of(mask):
+        need = sg.ROW_ENUM if mask else sg.ROW_LIST
+        return int((((flags_h & need) != 0) & ((bloom_h & np.uint64(mask)) == np.uint64(mask))).sum())
+
+    def device_step(i, mask, qsrc=None):
+        p = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask)
+        qptr = (qsrc if qsrc is not None else q_dev[i % N_QUERIES]).data_ptr()
+        m.search_device(p, qptr, out_dev.data_ptr(), k, cnt_dev.data_ptr(), stream)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, out_dev)
+            dist.all_gather_into_tensor(gcnt, cnt_dev)
+            m.merge_topk_device(gathered.data_ptr(), gcnt.data_ptr(), world, k, sg.ORDER_COSINE, k,
+                                fin_dev.data_ptr(), fcnt_dev.data_ptr(), stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_device(mask, steps, warmup):
+        for i in range(warmup):
+            device_step(i, mask)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = m.launch_count()
+        e0.record()
+        for i in range(steps):
+            device_step(i, mask)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = m.launch_count() - l0
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps, launches
+
+    def timed_e2e(mask, steps, warmup):
+        """host query in pinned memory -> H2D, scan (+ gather/merge), D2H of the hits, every step"""
+        qbuf = torch.empty(DIM, dtype=torch.float32, device=dev)
+
+        def one(i):
+            if single:
+                m.search(q_host[i % N_QUERIES], k, bloom_mask=mask)  # the host-buffer C-ABI call itself
+            else:
+                qbuf.copy_(q_pin[i % N_QUERIES], non_blocking=True)
+                device_step(i, mask, qsrc=qbuf)
+                res_pin.copy_(fin_dev, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+        for i in range(warmup):
+            one(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(steps):
+            one(i)
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return dt / steps * 1e3
+
+    head_mask = C2_MASK if single else 0
+    n_pass_local = n_pass_of(head_mask)
+    if world > 1:
+        t = torch.tensor([n_pass_local], device=dev, dtype=torch.int64)
+        dist.all_reduce(t)
+        n_pass_total = int(t.item())
+    else:
+        n_pass_total = n_pass_local
+    job_bytes = algorithmic_bytes(total_rows, n_pass_total)
+
+    with ClockSampler(local_rank) as clk:
+        ms_step, launches = timed_device(head_mask, args.steps, args.warmup)
+    clocks = clk.summary()
+    ms_e2e = timed_e2e(head_mask, args.steps, args.warmup)
+
+    variants = {}
+    if single:
+        for name, mask in (("mask_all_match_bit63", 1 << 63), ("unfiltered_mask_0", 0)):
+            ms_v, _ = timed_device(mask, args.steps, args.warmup)
+            b = algorithmic_bytes(total_rows, n_pass_of(mask))
+            variants[name] = {"ms_per_step": round(ms_v, 4), "queries_per_s": round(1e3 / ms_v, 2),
+                              "scanned_GB_per_s": round(b / ms_v / 1e6, 1), "roofline_frac": round(b / ms_v / 1e6 / peak, 4),
+                              "algorithmic_bytes": b}
+
+    # ---- parity gate on the timed configuration (rank-local shard sample vs oracle) ----
+    parity = parity_gate(m, sg, support, rows, row0, k, head_mask)
+
+    if rank == 0:
+        gbs = job_bytes / ms_step / 1e6
+        per_gpu_bytes = job_bytes / world
+        traffic = None
+        tp = ROOT / "profiles" / "roofline_traffic.json"
+        if tp.exists():
+            traffic = json.loads(tp.read_text()).get("c2_mask3_dram_bytes_per_launch" if single else "c4_dram_bytes_per_launch")
+        line = {
+            "metric": "scanned_GB_per_s", "value": round(gbs, 2), "unit": "GB/s",
+            "queries_per_s": round(1e3 / ms_step, 2),
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 5),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(world),
+            "e2e": {"value": round(job_bytes / ms_e2e / 1e6, 2), "unit": "GB/s", "queries_per_s": round(1e3 / ms_e2e, 2),
+                    "ms_per_step": round(ms_e2e, 5), "h2d_bytes_per_step": 4 * DIM, "d2h_bytes_per_step": 32 * k + 4},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": round(per_gpu_bytes / ms_step / 1e6, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(per_gpu_bytes / ms_step / 1e6 / peak, 4), "traffic": traffic,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": int(per_gpu_bytes),
+                         "kernel": "spl::scan_*_kernel (one launch per query per GPU)"},
+            "parity": parity,
+        }
+        if variants:
+            line["variants"] = variants
+        if single and not args.skip_cpu:
+            line["cpu_baseline"] = cpu_baseline_leg(k, head_mask)
+        print(json.dumps(line))
+    m.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def parity_gate(m, sg, support, rows, row0, k, mask):
+    """Re-score what the GPU returned with the oracle (rows regenerated from the counter RNG) and run one
+    full oracle search over the first 2^17 slots of this rank's shard."""
+    sample = min(rows, 1 << 17)
+    E, bloom, flags = support.synth_dense(SEED_CORPUS, SEED_BLOOM, row0, sample, DIM)
+    q = support.synth_queries(SEED_QUERY, 1, DIM)
+    with sg.Mirror.open_dense(sample, DIM, global_row0=row0, device=m.info().device) as ms:
+        ms.fill_synthetic(SEED_CORPUS, SEED_BLOOM)
+        out, cnt = ms.search(q, k, bloom_mask=mask)
+    ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=k, bloom_mask=mask)
+    got = out[0][:cnt[0]].copy()
+    got["slot_idx"] -= row0
+    try:
+        support.assert_topk_matches(got, ref[0][:rc[0]], exact=False)
+        idx_equal = bool(np.array_equal(got["slot_idx"], ref[0][:rc[0]]["idx"]))
+        return {"checked_slots": sample, "ok": True, "indices_identical": idx_equal,
+                "max_abs_dsim": float(np.max(np.abs(got["similarity"] - ref[0][:rc[0]]["similarity"]))) if len(got) else 0.0,
+                "max_rel_ddist": float(np.max(np.abs(got["distance"] - ref[0][:rc[0]]["distance"]) / ref[0][:rc[0]]["distance"])) if len(got) else 0.0}
+    except AssertionError as e:
+        return {"checked_slots": sample, "ok": False, "error": str(e)[:200]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs only)")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -14,6 +14,7 @@
 #include <float.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
@@ -106,6 +107,8 @@ struct spl_gpu_ctx {
     // bookkeeping
     std::mutex mu;  // serialises enqueueing on `stream` and the scratch above
     std::atomic<uint64_t> launches{0};
+    bool force_ldg = false;
+    unsigned long long *d_dbg = nullptr;  // SPL_GPU_DEBUG_TIMELINE=1: per-CTA timestamps of the last scan
     bool timing = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_scan_ms = -1.0;
@@ -132,6 +135,13 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreate(&c->ev0));
     CUDA_TRY(cudaEventCreate(&c->ev1));
+    CUDA_TRY(scan_tma_prepare());
+    const char *impl = getenv("SPL_GPU_SCAN_IMPL");  // developer knob: "ldg" forces the register-path kernel
+    c->force_ldg = impl && strcmp(impl, "ldg") == 0;
+    if (getenv("SPL_GPU_DEBUG_TIMELINE")) {
+        CUDA_TRY(cudaMalloc((void **)&c->d_dbg, 1024 * 4 * sizeof(unsigned long long)));
+        CUDA_TRY(cudaMemset(c->d_dbg, 0, 1024 * 4 * sizeof(unsigned long long)));
+    }
     return 0;
 }
 
@@ -313,6 +323,16 @@ extern "C" int spl_gpu_get_info(const spl_gpu_ctx *c, spl_gpu_info *out) {
     out->is_dense = c->dense;
     out->hbm_bytes = c->hbm_bytes;
     return 0;
+}
+
+// developer aid, not part of the public header: dump the per-CTA timeline of the last TMA scan
+extern "C" int spl_gpu_debug_timeline(spl_gpu_ctx *c, unsigned long long *out, int max_ctas) {
+    if (!c || !c->d_dbg) return -1;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    int n = max_ctas < c->sm_count ? max_ctas : c->sm_count;
+    cudaMemcpy(out, c->d_dbg, (size_t)n * 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    return n;
 }
 
 extern "C" uint64_t spl_gpu_launch_count(const spl_gpu_ctx *c) { return c ? c->launches.load() : 0; }
@@ -600,6 +620,7 @@ static void fill_args(const spl_gpu_ctx *c, const spl_gpu_search_params *p, Scan
         a.exclude = (uint32_t)(p->exclude_slot - c->slot_begin);
     a.row0 = c->slot_begin;
     a.cta_cands = c->d_cands; a.counters = c->d_counters;
+    a.dbg = c->d_dbg;
 }
 
 // enqueue one fused top-k scan per query (k in 1..KMAX_FUSED); caller holds c->mu
@@ -613,7 +634,8 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         a.q = d_q + (size_t)qi * c->dim;
         a.out = d_out + (size_t)qi * out_stride;
         a.out_count = d_counts + qi;
-        CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
+        if (!c->force_ldg && scan_tma_supported(a.dim, a.k)) CUDA_TRY(launch_scan_tma(a, c->sm_count, s));
+        else CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
         c->launches++;
     }
     return 0;

@@ -17,70 +17,11 @@
 // predicate) + 4*dim.  Rows are handed out dynamically in groups of 32 slots so a selective
 // mask does not unbalance the warps.
 #include "spl_scan.cuh"
+#include "spl_scan_epilogue.cuh"
 
 #include <float.h>
 
 namespace spl {
-
-// ---------------------------------------------------------------------------------------------
-// CTA epilogue shared by all single-query scan kernels: fold the kScanWarps per-warp lists into
-// one list per CTA, publish it, and let the last CTA to finish merge all CTAs' lists, sort the
-// survivors and write the result records.  Also re-arms the scratch counters for the next launch.
-// ---------------------------------------------------------------------------------------------
-__device__ void scan_epilogue(const ScanArgs &a, WarpTopK &W, uint64_t *skeys, uint32_t *sidx,
-                              uint32_t *s_flag) {
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t k = a.k;
-    __shared__ uint32_t s_cnt[kScanWarps];
-    if (lane == 0) s_cnt[warp] = W.cnt;
-    __syncthreads();
-    if (warp == 0) {
-        for (uint32_t w = 1; w < kScanWarps; w++) W.absorb(skeys + w * k, sidx + w * k, s_cnt[w], lane);
-        Cand *dst = a.cta_cands + (size_t)blockIdx.x * k;
-        for (uint32_t p = lane; p < k; p += kWarp) {
-            Cand c;
-            c.key = p < W.cnt ? W.keys[p] : kKeySentinel;
-            c.idx = p < W.cnt ? W.idxs[p] : kIdxSentinel;
-            c.pad = 0;
-            dst[p] = c;
-        }
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) {
-            uint32_t ticket = atomicAdd(&a.counters[1], 1u);
-            *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
-        }
-    }
-    __syncthreads();
-    if (*s_flag == 0) return;
-
-    // ---- last CTA: merge gridDim.x lists of k ----
-    __threadfence();
-    W.init(skeys + warp * k, sidx + warp * k, k);
-    for (uint32_t c = warp; c < gridDim.x; c += kScanWarps) W.absorb(a.cta_cands + (size_t)c * k, k, lane);
-    if (lane == 0) s_cnt[warp] = W.cnt;
-    __syncthreads();
-    if (warp == 0) {
-        for (uint32_t w = 1; w < kScanWarps; w++) W.absorb(skeys + w * k, sidx + w * k, s_cnt[w], lane);
-        if (lane == 0) { s_cnt[0] = W.cnt; a.counters[0] = 0; a.counters[1] = 0; *a.out_count = W.cnt; }
-    }
-    __syncthreads();
-    // rank sort: entry t goes to position (#entries that beat it); k <= blockDim.x * iterations
-    const uint32_t cnt = s_cnt[0];
-    for (uint32_t t = threadIdx.x; t < cnt; t += blockDim.x) {
-        const uint64_t key = skeys[t];
-        const uint32_t idx = sidx[t];
-        uint32_t rank = 0;
-        for (uint32_t j = 0; j < cnt; j++) rank += better(skeys[j], sidx[j], key, idx) ? 1u : 0u;
-        spl_gpu_result r;
-        split_key(a.order, key, r.similarity, r.distance);
-        r.slot_idx = (uint32_t)(a.row0 + idx);
-        r.has_embedding = (a.flags[idx] & SPL_ROW_EMB) ? 1u : 0u;
-        r.epoch = a.epoch[idx];
-        r.bloom = a.bloom[idx];
-        a.out[rank] = r;
-    }
-}
 
 // ---------------------------------------------------------------------------------------------
 // SPL_MODE_FAST: one warp per row, V float4 per lane (dim = 128*V), two rows in flight.
@@ -90,10 +31,13 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_kernel(const ScanAr
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_flag;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // lists region doubles as the final-merge workspace: ws entries, keys then idx
+    const uint32_t ws = KEYS ? 0u : scan_fast_ws_entries(a.k);
     uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + (size_t)kScanWarps * a.k);
+    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + ws);
     WarpTopK W;
     W.init(skeys + warp * a.k, sidx + warp * a.k, a.k);
+    if (!KEYS) { topk_lists_init(skeys, sidx, ws); __syncthreads(); }
 
     // query -> registers; |q|^2 once per warp
     const float4 *q4 = reinterpret_cast<const float4 *>(a.q);
@@ -211,7 +155,7 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_kernel(const ScanAr
         }
         return;
     }
-    scan_epilogue(a, W, skeys, sidx, &s_flag);
+    scan_epilogue<kScanWarps>(a, skeys, sidx, skeys, sidx, ws, &s_flag);
 }
 
 // generic dimension (dim % 4 == 0): query in shared memory, strided float4 loop, one row at a time
@@ -220,11 +164,13 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_generic_kernel(cons
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_flag;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t ws = KEYS ? 0u : scan_fast_ws_entries(a.k);
     uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + (size_t)kScanWarps * a.k);
-    float4 *sq = reinterpret_cast<float4 *>(smem_raw + ((scan_topk_smem(a.k) + 15) & ~(size_t)15));
+    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + ws);
+    float4 *sq = reinterpret_cast<float4 *>(smem_raw + (((size_t)ws * 12 + 15) & ~(size_t)15));
     WarpTopK W;
     W.init(skeys + warp * a.k, sidx + warp * a.k, a.k);
+    if (!KEYS) topk_lists_init(skeys, sidx, ws);
     const uint32_t nv = a.dim >> 2;
     for (uint32_t c = threadIdx.x; c < nv; c += blockDim.x) sq[c] = reinterpret_cast<const float4 *>(a.q)[c];
     __syncthreads();
@@ -291,14 +237,14 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_generic_kernel(cons
         }
         return;
     }
-    scan_epilogue(a, W, skeys, sidx, &s_flag);
+    scan_epilogue<kScanWarps>(a, skeys, sidx, skeys, sidx, ws, &s_flag);
 }
 
 int scan_fast_ctas_per_sm(uint32_t, uint32_t) { return 3; }
 
 template <bool KEYS>
 static cudaError_t launch_scan_fast_t(const ScanArgs &a, int grid, cudaStream_t stream) {
-    const size_t smem = KEYS ? 0 : scan_topk_smem(a.k);
+    const size_t smem = KEYS ? 0 : (size_t)scan_fast_ws_entries(a.k) * 12;
     if (a.dim == 768) {
         scan_fast_kernel<6, KEYS><<<grid, kScanThreads, smem, stream>>>(a);
     } else if (a.dim == 1024) {
@@ -321,72 +267,54 @@ cudaError_t launch_scan_fast(const ScanArgs &a, int grid, cudaStream_t stream) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// merge of result-record lists (after the per-GPU all-gather): one CTA
+// merge of result-record lists (after the per-GPU all-gather): one CTA, one bitonic sort
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kScanThreads, 1)
+constexpr uint32_t kMergeMaxEntries = 8192;  // nlists * stride candidates per call (96 KB of smem)
+
+__global__ void __launch_bounds__(1024, 1)
 merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t stride,
-                     uint32_t order, uint32_t k, spl_gpu_result *out, uint32_t *out_count) {
+                     uint32_t order, uint32_t k, uint32_t entries, spl_gpu_result *out, uint32_t *out_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ uint32_t s_cnt[kScanWarps];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + (size_t)kScanWarps * k);
-    // the payload index carried through the lists is the flat record position l*stride+i; ties are
-    // broken by the record's global slot index, which is what `better` must see, so we carry the
-    // slot index in idx and find the record again by (key, slot) afterwards.
-    WarpTopK W;
-    W.init(skeys + warp * k, sidx + warp * k, k);
-    for (uint32_t l = warp; l < nlists; l += kScanWarps) {
-        const uint32_t n = min(counts[l], stride);
-        for (uint32_t base = 0; base < n; base += kWarp) {
-            const uint32_t p = base + lane;
-            uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
-            if (p < n) {
-                const spl_gpu_result r = lists[(size_t)l * stride + p];
-                key = make_key(order, r.similarity, r.distance);
-                idx = r.slot_idx;
-            }
-            unsigned m = __ballot_sync(0xffffffffu, idx != kIdxSentinel && W.admits(key, idx));
-            while (m) {
-                const int s = __ffs(m) - 1; m &= m - 1;
-                W.insert(__shfl_sync(0xffffffffu, key, s), __shfl_sync(0xffffffffu, idx, s), lane);
-            }
+    uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
+    uint32_t *slot = reinterpret_cast<uint32_t *>(keys + entries);
+    uint32_t *pos = slot + entries;
+    for (uint32_t p = threadIdx.x; p < entries; p += blockDim.x) {
+        const uint32_t l = p / stride, i = p - l * stride;
+        uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
+        if (l < nlists && i < min(counts[l], stride)) {
+            const spl_gpu_result r = lists[p];
+            key = make_key(order, r.similarity, r.distance);
+            id = r.slot_idx;  // ties between shards break on the GLOBAL slot index
         }
-    }
-    if (lane == 0) s_cnt[warp] = W.cnt;
-    __syncthreads();
-    if (warp == 0) {
-        for (uint32_t w = 1; w < kScanWarps; w++) W.absorb(skeys + w * k, sidx + w * k, s_cnt[w], lane);
-        if (lane == 0) { s_cnt[0] = W.cnt; *out_count = W.cnt; }
+        keys[p] = key; slot[p] = id; pos[p] = p;
     }
     __syncthreads();
-    const uint32_t cnt = s_cnt[0];
-    // rank + recover the full record (epoch, bloom, has_embedding) from the source lists
-    for (uint32_t t = threadIdx.x; t < cnt; t += blockDim.x) {
-        const uint64_t key = skeys[t]; const uint32_t idx = sidx[t];
-        uint32_t rank = 0;
-        for (uint32_t j = 0; j < cnt; j++) rank += better(skeys[j], sidx[j], key, idx) ? 1u : 0u;
-        spl_gpu_result r;
-        r.slot_idx = idx; split_key(order, key, r.similarity, r.distance);
-        r.has_embedding = 1; r.epoch = 0; r.bloom = 0;
-        bool found = false;
-        for (uint32_t l = 0; l < nlists && !found; l++) {
-            const uint32_t n = min(counts[l], stride);
-            for (uint32_t i = 0; i < n; i++) {
-                const spl_gpu_result s = lists[(size_t)l * stride + i];
-                if (s.slot_idx == idx) { r.has_embedding = s.has_embedding; r.epoch = s.epoch; r.bloom = s.bloom;
-                                         r.similarity = s.similarity; r.distance = s.distance; found = true; break; }
-            }
-        }
-        out[rank] = r;
+    bitonic_sort_cta(keys, slot, entries, pos);
+    uint32_t cnt = 0;
+    for (uint32_t t = threadIdx.x; t < k; t += blockDim.x) {
+        if (slot[t] == kIdxSentinel) continue;
+        out[t] = lists[pos[t]];
+        if (t + 1 == k || slot[t + 1] == kIdxSentinel) cnt = t + 1;
     }
+    if (cnt) *out_count = cnt;
+    else if (threadIdx.x == 0 && slot[0] == kIdxSentinel) *out_count = 0;
 }
 
 cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,
                                  uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out,
                                  uint32_t *out_count, cudaStream_t stream) {
-    merge_results_kernel<<<1, kScanThreads, scan_topk_smem(k), stream>>>(lists, counts, nlists, stride, order, k,
-                                                                         out, out_count);
+    const uint32_t entries = topk_pow2(nlists * stride > k ? nlists * stride : k + 1);
+    if (entries > kMergeMaxEntries) return cudaErrorInvalidValue;
+    const size_t smem = (size_t)entries * 16;
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(merge_results_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(kMergeMaxEntries * 16));
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    const int threads = entries >= 2048 ? 1024 : (entries >= 512 ? 256 : 128);
+    merge_results_kernel<<<1, threads, smem, stream>>>(lists, counts, nlists, stride, order, k, entries, out, out_count);
     return cudaGetLastError();
 }
 

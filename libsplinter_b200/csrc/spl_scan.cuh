@@ -26,16 +26,38 @@ struct ScanArgs {
     // unlimited / large-k path: when non-null the kernel writes one key per surviving row here
     // (pre-filled with kKeySentinel by the caller) instead of keeping a top-k
     uint64_t *keys_out;
+    uint32_t chunk_groups;   // TMA kernel: 32-slot groups handed out per work-counter increment (1..8)
+    // developer timeline (nullable): per CTA {start, producers done, consumers done, end} in ns
+    unsigned long long *dbg;
 };
 
 constexpr int kScanThreads = 256;
 constexpr int kScanWarps = kScanThreads / 32;
 
-// smem bytes the fused top-k needs for a given k
-__host__ __device__ inline size_t scan_topk_smem(uint32_t k) { return (size_t)kScanWarps * k * (sizeof(uint64_t) + sizeof(uint32_t)); }
+__host__ __device__ inline uint32_t topk_pow2(uint32_t x) {
+    uint32_t p = 1;
+    while (p < x) p <<= 1;
+    return p;
+}
+// entries / bytes of the shared-memory region holding the per-warp top-k lists (padded to a power of
+// two so the epilogue can sort it in place): u64 keys[entries] followed by u32 idx[entries]
+__host__ __device__ inline uint32_t scan_topk_entries(uint32_t k, int nwarps = kScanWarps) { return topk_pow2((uint32_t)nwarps * k); }
+__host__ __device__ inline size_t scan_topk_smem(uint32_t k, int nwarps = kScanWarps) {
+    return (size_t)scan_topk_entries(k, nwarps) * (sizeof(uint64_t) + sizeof(uint32_t));
+}
+// the register-path kernel reuses its lists region as the final-merge workspace: at least 2048 entries
+__host__ __device__ inline uint32_t scan_fast_ws_entries(uint32_t k) {
+    const uint32_t p = scan_topk_entries(k);
+    return p > 2048u ? p : 2048u;
+}
 
 cudaError_t launch_scan_fast(const ScanArgs &a, int grid, cudaStream_t stream);
 int scan_fast_ctas_per_sm(uint32_t dim, uint32_t k);
+
+// TMA-staged variant (spl_scan_tma.cu): one persistent CTA per SM
+bool scan_tma_supported(uint32_t dim, uint32_t k);
+cudaError_t scan_tma_prepare();
+cudaError_t launch_scan_tma(const ScanArgs &a, int grid, cudaStream_t stream);
 
 // merge nlists lists of Cand-like results (spl_gpu_result records) into the top-k
 cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,

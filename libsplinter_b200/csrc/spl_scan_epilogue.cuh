@@ -1,0 +1,221 @@
+// spl_scan_epilogue.cuh -- the top-k epilogue every single-query scan kernel ends with.
+//
+// The reference sorts ALL survivors with qsort(compare_results) and prints the first `limit`
+// (/root/reference/splinter_cli_cmd_search.c:412-416).  Here each warp has kept a bounded
+// candidate list while scanning; the epilogue turns those lists into the same k rows:
+//   1. the CTA's NW lists (contiguous in shared memory, unused entries = sentinel) are sorted
+//      together by one block-wide bitonic network; the first k entries are the CTA's top-k;
+//   2. every CTA publishes its k entries; the LAST CTA to finish (ticket counter) gathers all
+//      gridDim.x * k published entries into a larger shared-memory workspace, sorts again and
+//      writes the k result records, already in the reference's order.
+#pragma once
+#include "spl_scan.cuh"
+
+namespace spl {
+
+__host__ __device__ inline uint32_t next_pow2(uint32_t x) {
+    uint32_t p = 1;
+    while (p < x) p <<= 1;
+    return p;
+}
+
+// Ascending bitonic sort of n = 2^m (key, idx) pairs in shared memory by the whole CTA.
+// Order is `better`: key ascending, then idx ascending.  `aux` (nullable) is carried along.
+__device__ __forceinline__ void bitonic_sort_cta(uint64_t *keys, uint32_t *idx, uint32_t n, uint32_t *aux = nullptr) {
+    for (uint32_t size = 2; size <= n; size <<= 1) {
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            for (uint32_t t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
+                const uint32_t i = ((t & ~(stride - 1)) << 1) | (t & (stride - 1));
+                const uint32_t j = i + stride;
+                const bool up = (i & size) == 0;
+                const uint64_t ki = keys[i], kj = keys[j];
+                const uint32_t ii = idx[i], ij = idx[j];
+                const bool j_first = better(kj, ij, ki, ii);
+                if (j_first == up) {
+                    keys[i] = kj; idx[i] = ij; keys[j] = ki; idx[j] = ii;
+                    if (aux) { const uint32_t x = aux[i]; aux[i] = aux[j]; aux[j] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ---- k <= 32: one (key, idx) per lane, everything in registers + shuffles -------------------
+// ascending bitonic sort of the 32 lane values
+__device__ __forceinline__ void warp_sort32(uint64_t &key, uint32_t &idx, uint32_t lane) {
+#pragma unroll
+    for (uint32_t size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            const uint64_t ok = __shfl_xor_sync(0xffffffffu, key, stride);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, idx, stride);
+            const bool up = (lane & size) == 0, lower = (lane & stride) == 0;
+            const bool other_first = better(ok, oi, key, idx);
+            if ((lower == up) ? other_first : !other_first) { key = ok; idx = oi; }
+        }
+    }
+}
+// a, b: two ascending 32-lane lists -> a := the 32 smallest of their union, ascending
+__device__ __forceinline__ void warp_merge32(uint64_t &key, uint32_t &idx, uint64_t bkey, uint32_t bidx, uint32_t lane) {
+    const uint64_t rk = __shfl_sync(0xffffffffu, bkey, 31 - lane);
+    const uint32_t ri = __shfl_sync(0xffffffffu, bidx, 31 - lane);
+    if (better(rk, ri, key, idx)) { key = rk; idx = ri; }  // bitonic sequence holding the 32 smallest
+#pragma unroll
+    for (uint32_t stride = 16; stride > 0; stride >>= 1) {
+        const uint64_t ok = __shfl_xor_sync(0xffffffffu, key, stride);
+        const uint32_t oi = __shfl_xor_sync(0xffffffffu, idx, stride);
+        const bool lower = (lane & stride) == 0;
+        const bool other_first = better(ok, oi, key, idx);
+        if (lower ? other_first : !other_first) { key = ok; idx = oi; }
+    }
+}
+// tree-merge the per-warp sorted lists of warps 0..NW-1 through `xk/xi` (NW*32 entries of smem);
+// afterwards warp 0 holds the CTA-wide top-32 (ascending).  Called by ALL threads of the CTA.
+template <int NW>
+__device__ __forceinline__ void cta_tree_merge32(uint64_t &key, uint32_t &idx, uint64_t *xk, uint32_t *xi) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int step = 1; step < NW; step <<= 1) {
+        if (warp < NW && (warp & (2 * step - 1)) == step) { xk[warp * 32 + lane] = key; xi[warp * 32 + lane] = idx; }
+        __syncthreads();
+        if (warp < NW && (warp & (2 * step - 1)) == 0 && warp + step < NW)
+            warp_merge32(key, idx, xk[(warp + step) * 32 + lane], xi[(warp + step) * 32 + lane], lane);
+        __syncthreads();
+    }
+}
+
+template <int NW>
+__device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t *skeys, uint32_t *sidx, uint32_t *s_flag) {
+    const uint32_t k = a.k, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    // 1. every list-holding warp sorts its own (unsorted, sentinel-padded) list
+    uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
+    if (warp < NW && lane < k) { key = skeys[warp * k + lane]; idx = sidx[warp * k + lane]; }
+    if (warp < NW) warp_sort32(key, idx, lane);
+    // 2. CTA top-32 by tree merge; the exchange buffer is a dedicated smem area passed by the caller
+    __shared__ uint64_t xk[NW * 32];
+    __shared__ uint32_t xi[NW * 32];
+    cta_tree_merge32<NW>(key, idx, xk, xi);
+    if (warp == 0 && lane < k) {
+        Cand c; c.key = key; c.idx = idx; c.pad = 0;
+        a.cta_cands[(size_t)blockIdx.x * k + lane] = c;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
+        *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (*s_flag == 0) return;
+    // 3. last CTA: each warp folds a strided subset of the gridDim.x published (sorted) lists
+    __threadfence();
+    key = kKeySentinel; idx = kIdxSentinel;
+    if (warp < NW) {
+        constexpr int kBatch = 8;  // lists loaded per round trip
+        for (uint32_t c0 = warp; c0 < gridDim.x; c0 += NW * kBatch) {
+            uint64_t bk[kBatch]; uint32_t bi[kBatch];
+#pragma unroll
+            for (int j = 0; j < kBatch; j++) {
+                const uint32_t c = c0 + j * NW;
+                bk[j] = kKeySentinel; bi[j] = kIdxSentinel;
+                if (c < gridDim.x && lane < k) {
+                    const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + (size_t)c * k + lane));
+                    bk[j] = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
+                    bi[j] = (uint32_t)raw.z;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kBatch; j++)
+                if (c0 + j * NW < gridDim.x) warp_merge32(key, idx, bk[j], bi[j], lane);
+        }
+    }
+    cta_tree_merge32<NW>(key, idx, xk, xi);
+    if (warp == 0) {
+        if (lane == 0) { a.counters[0] = 0; a.counters[1] = 0; }
+        const unsigned valid = __ballot_sync(0xffffffffu, lane < k && idx != kIdxSentinel);
+        if (lane == 0) *a.out_count = __popc(valid);
+        if (lane < k && idx != kIdxSentinel) {
+            spl_gpu_result r;
+            split_key(a.order, key, r.similarity, r.distance);
+            r.slot_idx = (uint32_t)(a.row0 + idx);
+            r.has_embedding = (a.flags[idx] & SPL_ROW_EMB) ? 1u : 0u;
+            r.epoch = a.epoch[idx];
+            r.bloom = a.bloom[idx];
+            a.out[lane] = r;
+        }
+    }
+}
+
+// workspace the final merge may use: `ws_entries` (power of two, >= 2*k) entries at ws_keys/ws_idx
+template <int NW>
+__device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys, uint32_t *sidx, uint64_t *ws_keys,
+                                              uint32_t *ws_idx, uint32_t ws_entries, uint32_t *s_flag) {
+    const uint32_t k = a.k;
+    if (k <= 32) { scan_epilogue_small<NW>(a, skeys, sidx, s_flag); return; }  // registers + shuffles
+    const uint32_t P = next_pow2(NW * k);  // the lists region is padded to P entries (sentinel-filled)
+    __syncthreads();
+    bitonic_sort_cta(skeys, sidx, P);
+    {
+        Cand *dst = a.cta_cands + (size_t)blockIdx.x * k;
+        for (uint32_t p = threadIdx.x; p < k; p += blockDim.x) {
+            Cand c;
+            c.key = skeys[p]; c.idx = sidx[p]; c.pad = 0;
+            dst[p] = c;
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
+        *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (*s_flag == 0) return;
+
+    // ---- last CTA: running top-k over gridDim.x * k published candidates, a workspace-full at a time ----
+    __threadfence();
+    const uint32_t total = gridDim.x * k;
+    const uint32_t need = next_pow2(total + k);
+    const uint32_t W = need < ws_entries ? need : ws_entries;  // workspace actually sorted
+    for (uint32_t p = threadIdx.x; p < k; p += blockDim.x) { ws_keys[p] = kKeySentinel; ws_idx[p] = kIdxSentinel; }
+    for (uint32_t base = 0; base < total; base += W - k) {
+        for (uint32_t p = k + threadIdx.x; p < W; p += blockDim.x) {
+            const uint32_t src = base + (p - k);
+            uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
+            if (src < total) {
+                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + src));
+                key = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
+                id = (uint32_t)raw.z;
+            }
+            ws_keys[p] = key; ws_idx[p] = id;
+        }
+        __syncthreads();
+        bitonic_sort_cta(ws_keys, ws_idx, W);  // running top-k stays in [0, k)
+    }
+    if (threadIdx.x == 0) { a.counters[0] = 0; a.counters[1] = 0; }
+    uint32_t cnt = 0;
+    for (uint32_t t = threadIdx.x; t < k; t += blockDim.x) {
+        const uint32_t idx = ws_idx[t];
+        if (idx == kIdxSentinel) continue;
+        spl_gpu_result r;
+        split_key(a.order, ws_keys[t], r.similarity, r.distance);
+        r.slot_idx = (uint32_t)(a.row0 + idx);
+        r.has_embedding = (a.flags[idx] & SPL_ROW_EMB) ? 1u : 0u;
+        r.epoch = a.epoch[idx];
+        r.bloom = a.bloom[idx];
+        a.out[t] = r;
+        // survivors are a prefix of the sorted array: the last valid one knows the count
+        if (t + 1 == k || ws_idx[t + 1] == kIdxSentinel) cnt = t + 1;
+    }
+    if (cnt) *a.out_count = cnt;
+    else if (threadIdx.x == 0 && ws_idx[0] == kIdxSentinel) *a.out_count = 0;
+}
+
+// sentinel-fill the padded lists region; every scan kernel calls this before its main loop
+__device__ __forceinline__ void topk_lists_init(uint64_t *skeys, uint32_t *sidx, uint32_t entries) {
+    for (uint32_t p = threadIdx.x; p < entries; p += blockDim.x) { skeys[p] = kKeySentinel; sidx[p] = kIdxSentinel; }
+}
+
+}  // namespace spl

@@ -1,0 +1,354 @@
+// spl_scan_tma.cu -- single-query fused scan, TMA-staged (the default SPL_MODE_FAST kernel).
+//
+// Same contract as spl_scan.cu (predicate -> cosine + L2 -> thresholds -> top-k; reference:
+// /root/reference/splinter_cli_cmd_search.c:336-416) but the embedding rows travel HBM -> shared
+// memory through the bulk-copy engine (cp.async.bulk, SASS UBLKCP) instead of through registers:
+//
+//   producer warp    evaluates the label / validity predicate for 32 slots at a time from 9 bytes
+//                    per slot (bloom u64 + flags u8) and, only for the slots that pass, issues bulk
+//                    copies of the rows into a shared-memory ring of PAIR slots (2 rows each; two
+//                    passing rows that are neighbours in HBM travel as one 8*dim-byte copy).  Rows
+//                    that fail the predicate never leave HBM.
+//   16 consumer warps each take every 16th pair slot: wait on the slot's mbarrier, pull both rows
+//                    into registers with conflict-free 128-bit LDS, hand the slot back, then score
+//                    the two rows interleaved (dot, |e|^2, sum (q-e)^2, warp-shuffle tree) and feed
+//                    the per-warp top-k list.
+//
+// One persistent CTA per SM keeps up to 192 KB of row data in flight per SM no matter what the
+// compute warps are doing -- what an HBM-bound gather of 3 KB rows needs.
+#include <float.h>
+
+#include "spl_scan.cuh"
+#include "spl_scan_epilogue.cuh"
+
+namespace spl {
+
+constexpr int kConsumers = 16;
+constexpr int kProducers = 4;
+constexpr int kTmaThreads = (kConsumers + kProducers) * 32;  // consumers = warps 0..15, producers = warps 16..19
+constexpr uint32_t kSmemBudget = 227u * 1024u;
+constexpr uint32_t kMaxPairs = 32;
+constexpr uint32_t kMinPairs = 17;  // a 32-slot group may straddle 17 pair slots; all must be distinct
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+// Slot hand-back uses an exact generation count instead of an mbarrier parity: with several
+// producer warps one of them may run a whole ring ahead of another, which a 1-bit phase cannot
+// tell apart from "the previous round".
+__device__ __forceinline__ void wait_gen(uint32_t addr, uint32_t gen) {
+    uint32_t v;
+    do {
+        asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    } while (v != gen);
+}
+__device__ __forceinline__ void publish_gen(uint32_t addr, uint32_t gen) {
+    asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(addr), "r"(gen) : "memory");
+}
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+struct TmaLayout {
+    uint32_t pairs, row_bytes, rows_off, full_off, empty_off, meta_off, total;
+};
+
+__host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k) {
+    TmaLayout L;
+    L.row_bytes = dim * 4;
+    const uint32_t topk = (uint32_t)scan_topk_smem(k, kConsumers);
+    L.full_off = (topk + 15u) & ~15u;                             // top-k lists sit at offset 0
+    L.empty_off = L.full_off + kMaxPairs * 8;
+    L.meta_off = L.empty_off + kMaxPairs * 8;                     // uint4 {row0, flags0, row1, flags1}
+    L.rows_off = (L.meta_off + kMaxPairs * 16 + 127u) & ~127u;
+    const uint32_t avail = kSmemBudget - 8192u - L.rows_off;      // 8 KB headroom for static smem
+    const uint32_t p = avail / (2 * L.row_bytes);
+    L.pairs = p > kMaxPairs ? kMaxPairs : p;
+    L.total = L.rows_off + L.pairs * 2 * L.row_bytes;
+    return L;
+}
+
+template <int V>
+__global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint32_t s_flag;
+    __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const TmaLayout L = tma_layout(a.dim, a.k);
+    const uint32_t list_entries = scan_topk_entries(a.k, kConsumers);
+    uint64_t *skeys = reinterpret_cast<uint64_t *>(smem);
+    uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + list_entries);
+    const uint32_t full0 = smem_u32(smem + L.full_off), empty0 = smem_u32(smem + L.empty_off);
+    uint4 *meta = reinterpret_cast<uint4 *>(smem + L.meta_off);
+    const uint32_t NP = L.pairs, RB = L.row_bytes;
+
+    if (threadIdx.x == 0) {
+        if (a.dbg) a.dbg[blockIdx.x * 4 + 0] = gtime();
+        s_seq = 0;
+        for (uint32_t s = 0; s < NP; s++) { mbar_init(full0 + 8 * s, 2); publish_gen(empty0 + 8 * s, 0); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    topk_lists_init(skeys, sidx, list_entries);
+    __syncthreads();
+
+    WarpTopK W;
+    W.init(skeys + (warp < kConsumers ? warp : 0) * a.k, sidx + (warp < kConsumers ? warp : 0) * a.k, a.k);
+
+    if (warp >= kConsumers) {
+        // ================================ producers ================================
+        // kProducers warps run the same loop on different chunks; ring positions are handed out
+        // by one shared-memory atomic per 32-slot group, so the rows of all producers interleave
+        // into one sequence that the consumers drain in order.
+        const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+        const uint32_t ngroups = (a.n + 31u) >> 5;
+        const unsigned char *Eb = reinterpret_cast<const unsigned char *>(a.E);
+        const uint32_t rows_s = smem_u32(smem + L.rows_off);
+        // Work is handed out in chunks of kChunk groups (kChunk*32 slots) by one atomic per chunk
+        // (a single counter cannot sustain one atomic per 32 slots at HBM speed).  The NEXT chunk's
+        // base and its predicate bytes are requested before the current chunk's rows are issued, so
+        // neither the atomic's round trip nor the 9-byte-per-slot reads sit on the critical path.
+        // The loop body is written out twice (register sets A / B) so the prefetched registers are
+        // never copied -- a copy would wait for the loads it is meant to hide.
+        constexpr int kChunk = 8;
+        const uint32_t cg = a.chunk_groups;  // groups per chunk actually used (small stores use small chunks)
+        const uint32_t nchunks = (ngroups + cg - 1) / cg;
+        auto fetch_chunk = [&]() -> uint32_t {
+            uint32_t c = 0;
+            if (lane == 0) c = atomicAdd(&a.counters[0], 1u);
+            return c;  // lane 0 only; broadcast lazily so the atomic's latency is not exposed here
+        };
+        auto load_chunk_pred = [&](uint32_t c, uint32_t (&f)[kChunk], uint64_t (&b)[kChunk]) {
+#pragma unroll
+            for (int j = 0; j < kChunk; j++) {
+                const uint32_t row = ((c * cg + j) << 5) + lane;
+                f[j] = 0; b[j] = 0;
+                if (j < cg && c < nchunks && row < a.n) { f[j] = a.flags[row]; b[j] = a.bloom[row]; }
+            }
+        };
+        auto issue_chunk = [&](uint32_t c, const uint32_t (&f)[kChunk], const uint64_t (&b)[kChunk]) {
+#pragma unroll
+            for (int j = 0; j < kChunk; j++) {
+                const uint32_t row = ((c * cg + j) << 5) + lane;
+                const bool pass = (f[j] & need) && ((b[j] & a.mask) == a.mask) && row != a.exclude;
+                const unsigned m = __ballot_sync(0xffffffffu, pass);
+                if (m == 0) continue;
+                uint32_t seq = 0;
+                if (lane == 0) seq = atomicAdd(&s_seq, (uint32_t)__popc(m));
+                seq = __shfl_sync(0xffffffffu, seq, 0);
+                if (pass) {
+                    const uint32_t my = seq + __popc(m & ((1u << lane) - 1u));
+                    const uint32_t sub = my & 1u;
+                    const uint32_t pair = my >> 1;
+                    const uint32_t gen = pair / NP, slot = pair - gen * NP;
+                    const uint32_t fullb = full0 + 8 * slot;
+                    const uint32_t dst = rows_s + (slot * 2 + sub) * RB;
+                    const unsigned char *src = Eb + (size_t)row * RB;
+                    // Every lane waits for the slot's previous round to be handed back before it touches
+                    // the slot's metadata or rows (the two rows of a pair may be issued by different lanes,
+                    // in either order once the warp diverges).
+                    wait_gen(empty0 + 8 * slot, gen);
+                    if (sub == 0) {
+                        // first row of a pair opens the slot.  If the next lane passes too it holds
+                        // row+1 at position my+1: one contiguous 2*RB burst covers both.
+                        const bool next_adjacent = lane < 31 && ((m >> (lane + 1)) & 1u);
+                        meta[slot].x = row; meta[slot].y = f[j];
+                        mbar_arrive_expect_tx(fullb, next_adjacent ? 2 * RB : RB);
+                        bulk_g2s(dst, src, next_adjacent ? 2 * RB : RB, fullb);
+                    } else {
+                        // second row: the slot was opened by the pair's first row (possibly in an earlier
+                        // group).  If that first row sits in the previous lane it has copied this row too.
+                        const bool prev_adjacent = lane > 0 && ((m >> (lane - 1)) & 1u);
+                        meta[slot].z = row; meta[slot].w = f[j];
+                        if (prev_adjacent) {
+                            mbar_arrive(fullb);
+                        } else {
+                            mbar_arrive_expect_tx(fullb, RB);
+                            bulk_g2s(dst, src, RB, fullb);
+                        }
+                    }
+                }
+            }
+        };
+        uint32_t cA = __shfl_sync(0xffffffffu, fetch_chunk(), 0);
+        uint32_t fA[kChunk], fB[kChunk]; uint64_t bA[kChunk], bB[kChunk];
+        load_chunk_pred(cA, fA, bA);
+        uint32_t next_raw = fetch_chunk();
+        while (cA < nchunks) {
+            const uint32_t cB = __shfl_sync(0xffffffffu, next_raw, 0);
+            load_chunk_pred(cB, fB, bB);
+            next_raw = fetch_chunk();
+            issue_chunk(cA, fA, bA);
+            if (cB >= nchunks) break;
+            cA = __shfl_sync(0xffffffffu, next_raw, 0);
+            load_chunk_pred(cA, fA, bA);
+            next_raw = fetch_chunk();
+            issue_chunk(cB, fB, bB);
+        }
+        // ---- end of stream: wait for the other producers, then one warp closes the sequence ----
+        asm volatile("bar.sync 1, %0;" ::"n"(kProducers * 32) : "memory");
+        if (a.dbg && threadIdx.x == kConsumers * 32) a.dbg[blockIdx.x * 4 + 1] = gtime();
+        if (warp == kConsumers) {
+            const uint32_t seq = *reinterpret_cast<volatile uint32_t *>(&s_seq);
+            uint32_t pair = seq >> 1;
+            if (seq & 1u) {  // a half-filled pair: close it with an empty second row
+                if (lane == 0) {
+                    const uint32_t slot = pair % NP;
+                    meta[slot].z = kIdxSentinel; meta[slot].w = 0;
+                    mbar_arrive(full0 + 8 * slot);
+                }
+                pair++;
+            }
+            if (lane < kConsumers) {  // one sentinel pair per consumer
+                pair += lane;
+                const uint32_t gen = pair / NP, slot = pair - gen * NP;
+                wait_gen(empty0 + 8 * slot, gen);
+                meta[slot] = make_uint4(kIdxSentinel, 0, kIdxSentinel, 0);
+                mbar_arrive(full0 + 8 * slot);
+                mbar_arrive(full0 + 8 * slot);
+            }
+        }
+    } else {
+        // ================================ consumers ================================
+        const float4 *q4 = reinterpret_cast<const float4 *>(a.q);
+        float4 qv[V];
+        float ma = 0.f;
+#pragma unroll
+        for (int j = 0; j < V; j++) {
+            qv[j] = q4[j * 32 + lane];
+            ma = fmaf(qv[j].x, qv[j].x, ma); ma = fmaf(qv[j].y, qv[j].y, ma);
+            ma = fmaf(qv[j].z, qv[j].z, ma); ma = fmaf(qv[j].w, qv[j].w, ma);
+        }
+        ma = warp_sum(ma);
+        const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+        auto finish = [&](uint32_t row, uint32_t f, float dot, float mb, float ss) {
+            float sim, dist;
+            if (f & SPL_ROW_EMB) {
+                sim = cosine_from_sums(dot, ma, mb);
+                dist = __fsqrt_rn(ss);
+                if (a.min_sim > 0.f && sim < a.min_sim) return;
+                if (a.max_dist > 0.f && dist > a.max_dist) return;
+            } else {  // _search.c:388-393
+                if (thresholds) return;
+                sim = 0.f; dist = FLT_MAX;
+            }
+            const uint64_t key = make_key(a.order, sim, dist);
+            if (W.admits(key, row)) W.insert(key, row, lane);
+        };
+        uint32_t slot = warp, gen = 0;  // this warp's pair index = gen * NP + slot
+        if (slot >= NP) { slot -= NP; gen++; }
+        for (;;) {
+            mbar_wait(full0 + 8 * slot, gen & 1u);
+            const uint4 mt = meta[slot];
+            if (mt.x == kIdxSentinel) break;
+            const float4 *r0 = reinterpret_cast<const float4 *>(smem + L.rows_off + (size_t)slot * 2 * RB) + lane;
+            const float4 *r1 = reinterpret_cast<const float4 *>(reinterpret_cast<const unsigned char *>(r0) + RB);
+            const bool two = mt.z != kIdxSentinel;
+            float4 x[V], y[V];
+#pragma unroll
+            for (int j = 0; j < V; j++) x[j] = r0[32 * j];
+#pragma unroll
+            for (int j = 0; j < V; j++) y[j] = two ? r1[32 * j] : x[j];
+            __syncwarp();
+            if (lane == 0) publish_gen(empty0 + 8 * slot, gen + 1);  // both rows now live in registers
+            slot += kConsumers;
+            if (slot >= NP) { slot -= NP; gen++; }
+            float d0 = 0.f, e0 = 0.f, s0 = 0.f, d1 = 0.f, e1 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < V; j++) {
+                float t, u;
+                d0 = fmaf(qv[j].x, x[j].x, d0); e0 = fmaf(x[j].x, x[j].x, e0); t = qv[j].x - x[j].x; s0 = fmaf(t, t, s0);
+                d1 = fmaf(qv[j].x, y[j].x, d1); e1 = fmaf(y[j].x, y[j].x, e1); u = qv[j].x - y[j].x; s1 = fmaf(u, u, s1);
+                d0 = fmaf(qv[j].y, x[j].y, d0); e0 = fmaf(x[j].y, x[j].y, e0); t = qv[j].y - x[j].y; s0 = fmaf(t, t, s0);
+                d1 = fmaf(qv[j].y, y[j].y, d1); e1 = fmaf(y[j].y, y[j].y, e1); u = qv[j].y - y[j].y; s1 = fmaf(u, u, s1);
+                d0 = fmaf(qv[j].z, x[j].z, d0); e0 = fmaf(x[j].z, x[j].z, e0); t = qv[j].z - x[j].z; s0 = fmaf(t, t, s0);
+                d1 = fmaf(qv[j].z, y[j].z, d1); e1 = fmaf(y[j].z, y[j].z, e1); u = qv[j].z - y[j].z; s1 = fmaf(u, u, s1);
+                d0 = fmaf(qv[j].w, x[j].w, d0); e0 = fmaf(x[j].w, x[j].w, e0); t = qv[j].w - x[j].w; s0 = fmaf(t, t, s0);
+                d1 = fmaf(qv[j].w, y[j].w, d1); e1 = fmaf(y[j].w, y[j].w, e1); u = qv[j].w - y[j].w; s1 = fmaf(u, u, s1);
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                d0 += __shfl_xor_sync(0xffffffffu, d0, off);
+                e0 += __shfl_xor_sync(0xffffffffu, e0, off);
+                s0 += __shfl_xor_sync(0xffffffffu, s0, off);
+                d1 += __shfl_xor_sync(0xffffffffu, d1, off);
+                e1 += __shfl_xor_sync(0xffffffffu, e1, off);
+                s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+            }
+            finish(mt.x, mt.y, d0, e0, s0);
+            if (two) finish(mt.z, mt.w, d1, e1, s1);
+        }
+    }
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 4 + 2] = gtime();
+    // the row ring is idle now: it becomes the workspace of the final cross-CTA merge
+    uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
+    uint64_t *ws_keys = reinterpret_cast<uint64_t *>(smem + L.rows_off);
+    uint32_t *ws_idx = reinterpret_cast<uint32_t *>(ws_keys + ws_entries);
+    scan_epilogue<kConsumers>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 4 + 3] = gtime();
+}
+
+bool scan_tma_supported(uint32_t dim, uint32_t k) {
+    if (dim != 768 && dim != 1024 && dim != 512 && dim != 256 && dim != 128) return false;
+    return tma_layout(dim, k).pairs >= kMinPairs;
+}
+
+template <int V>
+static cudaError_t launch_v(const ScanArgs &a, int grid, cudaStream_t stream) {
+    const TmaLayout L = tma_layout(a.dim, a.k);
+    scan_tma_kernel<V><<<grid, kTmaThreads, L.total, stream>>>(a);
+    return cudaGetLastError();
+}
+
+// opt in to > 48 KB dynamic shared memory; call once per device with that device current
+cudaError_t scan_tma_prepare() {
+    cudaError_t e;
+    const int bytes = (int)kSmemBudget - 8192;  // static smem (exchange buffers, flags) takes the rest
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    return cudaSuccess;
+}
+
+cudaError_t launch_scan_tma(const ScanArgs &a_in, int grid, cudaStream_t stream) {
+    ScanArgs a = a_in;
+    // aim for >= 4 chunks per producer warp so the dynamic hand-out can balance; cap at 8 groups
+    const uint32_t ngroups = (a.n + 31u) >> 5;
+    uint32_t cg = 8;
+    while (cg > 1 && ngroups / cg < (uint32_t)grid * kProducers * 4u) cg >>= 1;
+    a.chunk_groups = cg;
+    switch (a.dim) {
+        case 768: return launch_v<6>(a, grid, stream);
+        case 1024: return launch_v<8>(a, grid, stream);
+        case 512: return launch_v<4>(a, grid, stream);
+        case 256: return launch_v<2>(a, grid, stream);
+        case 128: return launch_v<1>(a, grid, stream);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace spl
