@@ -189,6 +189,34 @@ int spl_gpu_merge_topk_device(spl_gpu_ctx *ctx, const spl_gpu_result *d_lists, c
                               uint32_t nlists, uint32_t list_stride, uint32_t order, uint32_t k,
                               spl_gpu_result *d_out, uint32_t *d_out_count, void *stream);
 
+/* Allocation-free variant of the fused single-query scan.  (No counterpart in the reference; it
+ * exists only because of how GPU memory is managed.)
+ *
+ * For callers that cannot call cudaMalloc: hosts that gave all device memory to their own arena or
+ * pool, latency-critical loops that cannot take the device-wide stall an allocation implies, or
+ * processes whose device memory is full by design.  The caller passes everything as device pointers
+ * on the CURRENT device -- the mirror columns (E = n_rows x p->dim fp32 rows, bloom, flags with
+ * SPL_ROW_* bits, epoch), the query vector(s) and the result buffers -- and the kernel's scratch
+ * (per-CTA candidate lists + two counters) lives in a fixed 257 KB array inside the library image,
+ * which every GPU that loads the library holds until the process exits.
+ *
+ *  - Limits: 1 <= p->k <= 64; p->dim in {128, 256, 512, 768, 1024}; p->mode AUTO or FAST; at most
+ *    256 SMs.  Anything larger is refused with -2 / EINVAL and a message (use spl_gpu_search).
+ *  - No cudaMalloc / cudaFree or other allocating call is made.  The FIRST call on a device looks
+ *    the array's device address up and configures the kernel; make that first call outside any
+ *    stream capture.
+ *  - All calls on a device share the one array and it keeps the previous call's contents; each call
+ *    clears the counters it needs at zero on `stream` before launching.  Two calls whose work
+ *    overlaps on the GPU (different streams, no dependency) race on the scratch and return garbage:
+ *    order them.
+ *  - Work is enqueued on `stream` (a cudaStream_t, may be NULL for the default stream); the call
+ *    does not synchronise.  Results: d_out[q * out_stride + i], d_counts[q], slot indices are
+ *    global_row0 + row. */
+int spl_gpu_scan_noalloc(const float *d_E, const uint64_t *d_bloom, const uint8_t *d_flags,
+                         const uint64_t *d_epoch, uint64_t n_rows, uint64_t global_row0,
+                         const spl_gpu_search_params *p, const float *d_q, spl_gpu_result *d_out,
+                         uint32_t out_stride, uint32_t *d_counts, void *stream);
+
 /* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
 uint64_t spl_gpu_launch_count(const spl_gpu_ctx *ctx);
 

@@ -49,6 +49,11 @@ static int fail(int rc, int err, const char *fmt, ...) {
     errno = err;
     return rc;
 }
+namespace spl {
+// lets other translation units report through spl_gpu_last_error()
+void set_last_error(const char *msg) { snprintf(g_err, sizeof g_err, "%s", msg); }
+}  // namespace spl
+
 #define CUDA_TRY(expr)                                                                                   \
     do {                                                                                                 \
         cudaError_t e__ = (expr);                                                                        \
