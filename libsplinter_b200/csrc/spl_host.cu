@@ -101,6 +101,8 @@ struct spl_gpu_ctx {
     float *d_q = nullptr, *h_q = nullptr;
     spl_gpu_result *d_out = nullptr, *h_out = nullptr;
     uint32_t *d_count = nullptr, *h_count = nullptr;
+    spl_gpu_result *m_out = nullptr;  // device views of the mapped host buffers h_out / h_count
+    uint32_t *m_count = nullptr;
     uint32_t q_cap = 0, out_cap = 0;
     // unlimited-k scratch (lazy)
     uint64_t *d_keys = nullptr;
@@ -182,8 +184,12 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     if ((rc = dev_alloc(c, &c->d_out, c->out_cap, false))) return rc;
     if ((rc = dev_alloc(c, &c->d_count, c->q_cap, true))) return rc;
     CUDA_TRY(cudaMallocHost((void **)&c->h_q, (size_t)c->q_cap * c->dim * sizeof(float)));
-    CUDA_TRY(cudaMallocHost((void **)&c->h_out, (size_t)c->out_cap * sizeof(spl_gpu_result)));
-    CUDA_TRY(cudaMallocHost((void **)&c->h_count, (size_t)c->q_cap * sizeof(uint32_t)));
+    // results land straight in mapped pinned host memory: the last CTA's few hundred bytes of stores
+    // cross PCIe inside the kernel, which saves two cudaMemcpyAsync round trips per search
+    CUDA_TRY(cudaHostAlloc((void **)&c->h_out, (size_t)c->out_cap * sizeof(spl_gpu_result), cudaHostAllocMapped));
+    CUDA_TRY(cudaHostAlloc((void **)&c->h_count, (size_t)c->q_cap * sizeof(uint32_t), cudaHostAllocMapped));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_out, c->h_out, 0));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_count, c->h_count, 0));
     // staging for sync / dense upload
     if (c->sync_threads == 0) {
         unsigned hc = std::thread::hardware_concurrency();
@@ -695,10 +701,8 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
             CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
-            if ((rc = enqueue_fused(c, &pp, c->d_q, c->d_out, p->k, c->d_count, c->stream))) return rc;
+            if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream))) return rc;
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
-            CUDA_TRY(cudaMemcpyAsync(c->h_out, c->d_out, (size_t)nq * p->k * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost, c->stream));
-            CUDA_TRY(cudaMemcpyAsync(c->h_count, c->d_count, nq * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
             CUDA_TRY(cudaStreamSynchronize(c->stream));
             if (c->timing) {
                 float ms = 0.f;

@@ -113,7 +113,7 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
     __threadfence();
     key = kKeySentinel; idx = kIdxSentinel;
     if (warp < NW) {
-        constexpr int kBatch = 8;  // lists loaded per round trip
+        constexpr int kBatch = 10;  // lists loaded per round trip (148 CTAs / 16 warps: one round)
         for (uint32_t c0 = warp; c0 < gridDim.x; c0 += NW * kBatch) {
             uint64_t bk[kBatch]; uint32_t bi[kBatch];
 #pragma unroll

@@ -73,7 +73,7 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 }
 
 struct TmaLayout {
-    uint32_t pairs, row_bytes, rows_off, full_off, empty_off, meta_off, total;
+    uint32_t pairs, row_bytes, rows_off, full_off, empty_off, meta_off, clist_off, total;
 };
 
 __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k) {
@@ -83,7 +83,8 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k) {
     L.full_off = (topk + 15u) & ~15u;                             // top-k lists sit at offset 0
     L.empty_off = L.full_off + kMaxPairs * 8;
     L.meta_off = L.empty_off + kMaxPairs * 8;                     // uint4 {row0, flags0, row1, flags1}
-    L.rows_off = (L.meta_off + kMaxPairs * 16 + 127u) & ~127u;
+    L.clist_off = L.meta_off + kMaxPairs * 16;                    // per producer warp: 256 x {row, flags}
+    L.rows_off = (L.clist_off + kProducers * 256 * 8 + 127u) & ~127u;
     const uint32_t avail = kSmemBudget - 8192u - L.rows_off;      // 8 KB headroom for static smem
     const uint32_t p = avail / (2 * L.row_bytes);
     L.pairs = p > kMaxPairs ? kMaxPairs : p;
@@ -148,48 +149,52 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                 if (j < cg && c < nchunks && row < a.n) { f[j] = a.flags[row]; b[j] = a.bloom[row]; }
             }
         };
+        // Rows that pass are first compacted into a per-warp list in shared memory, then issued 32 at a
+        // time by ONE convergent instruction sequence (wait for the slot, write its metadata, arm the
+        // mbarrier, bulk copy).  With a selective mask this turns ~8 short divergent sequences per chunk
+        // into one full-width pass; the long-latency steps (shared atomics, mbarrier ops, the per-lane
+        // serialised UBLKCP issue) are paid per pass, not per 32-slot group.
+        uint2 *clist = reinterpret_cast<uint2 *>(smem + L.clist_off) + (warp - kConsumers) * (kChunk * 32);
+        uint32_t *meta32 = reinterpret_cast<uint32_t *>(meta);
         auto issue_chunk = [&](uint32_t c, const uint32_t (&f)[kChunk], const uint64_t (&b)[kChunk]) {
+            uint32_t T = 0;
 #pragma unroll
             for (int j = 0; j < kChunk; j++) {
                 const uint32_t row = ((c * cg + j) << 5) + lane;
                 const bool pass = (f[j] & need) && ((b[j] & a.mask) == a.mask) && row != a.exclude;
                 const unsigned m = __ballot_sync(0xffffffffu, pass);
-                if (m == 0) continue;
-                uint32_t seq = 0;
-                if (lane == 0) seq = atomicAdd(&s_seq, (uint32_t)__popc(m));
-                seq = __shfl_sync(0xffffffffu, seq, 0);
-                if (pass) {
-                    const uint32_t my = seq + __popc(m & ((1u << lane) - 1u));
-                    const uint32_t sub = my & 1u;
-                    const uint32_t pair = my >> 1;
+                if (pass) clist[T + __popc(m & ((1u << lane) - 1u))] = make_uint2(row, f[j]);
+                T += __popc(m);
+            }
+            if (T == 0) return;
+            __syncwarp();  // clist writes -> reads by other lanes
+            uint32_t seq0 = 0;
+            if (lane == 0) seq0 = atomicAdd(&s_seq, T);
+            seq0 = __shfl_sync(0xffffffffu, seq0, 0);
+            for (uint32_t t0 = 0; t0 < T; t0 += 32) {
+                const uint32_t i = t0 + lane;
+                if (i < T) {
+                    const uint2 me = clist[i];
+                    const uint32_t my = seq0 + i, sub = my & 1u, pair = my >> 1;
                     const uint32_t gen = pair / NP, slot = pair - gen * NP;
                     const uint32_t fullb = full0 + 8 * slot;
-                    const uint32_t dst = rows_s + (slot * 2 + sub) * RB;
-                    const unsigned char *src = Eb + (size_t)row * RB;
-                    // Every lane waits for the slot's previous round to be handed back before it touches
-                    // the slot's metadata or rows (the two rows of a pair may be issued by different lanes,
-                    // in either order once the warp diverges).
+                    // a pair whose two rows are neighbours in HBM and sit in the same pass travels as one copy
+                    const bool next_adj = sub == 0 && lane < 31 && i + 1 < T && clist[i + 1].x == me.x + 1;
+                    const bool prev_adj = sub == 1 && lane > 0 && clist[i - 1].x + 1 == me.x;
+                    const uint32_t bytes = prev_adj ? 0u : (next_adj ? 2 * RB : RB);
+                    // every lane waits for the slot's previous round to be handed back before it touches
+                    // the slot's metadata or rows
                     wait_gen(empty0 + 8 * slot, gen);
-                    if (sub == 0) {
-                        // first row of a pair opens the slot.  If the next lane passes too it holds
-                        // row+1 at position my+1: one contiguous 2*RB burst covers both.
-                        const bool next_adjacent = lane < 31 && ((m >> (lane + 1)) & 1u);
-                        meta[slot].x = row; meta[slot].y = f[j];
-                        mbar_arrive_expect_tx(fullb, next_adjacent ? 2 * RB : RB);
-                        bulk_g2s(dst, src, next_adjacent ? 2 * RB : RB, fullb);
+                    meta32[slot * 4 + sub * 2] = me.x;
+                    meta32[slot * 4 + sub * 2 + 1] = me.y;
+                    if (bytes) {
+                        mbar_arrive_expect_tx(fullb, bytes);
+                        bulk_g2s(rows_s + (slot * 2 + sub) * RB, Eb + (size_t)me.x * RB, bytes, fullb);
                     } else {
-                        // second row: the slot was opened by the pair's first row (possibly in an earlier
-                        // group).  If that first row sits in the previous lane it has copied this row too.
-                        const bool prev_adjacent = lane > 0 && ((m >> (lane - 1)) & 1u);
-                        meta[slot].z = row; meta[slot].w = f[j];
-                        if (prev_adjacent) {
-                            mbar_arrive(fullb);
-                        } else {
-                            mbar_arrive_expect_tx(fullb, RB);
-                            bulk_g2s(dst, src, RB, fullb);
-                        }
+                        mbar_arrive(fullb);
                     }
                 }
+                __syncwarp();
             }
         };
         uint32_t cA = __shfl_sync(0xffffffffu, fetch_chunk(), 0);
