@@ -1,0 +1,472 @@
+// spl_batch.cu -- batched multi-query search as a dense Q x E^T contraction on the 5th-gen tensor
+// cores (SPL_MODE_BATCH_BF16, config C3).
+//
+// The reference scores one query at a time (cmd_search is one process per query,
+// /root/reference/splinter_cli_cmd_search.c:373-409); for nq queries the same arithmetic is
+// S[q][e] = sum_d Q[q][d] * E[e][d], a GEMM with M = nq, N = slots, K = D.  Scores are never
+// written out: the epilogue turns every accumulator element into an ordering value and keeps
+// only the few that can still reach the top-k.
+//
+//   gemm_topk_kernel  persistent, one CTA per SM, warp-specialised:
+//       warp 0   TMA producer: Q tile (128 x 64 bf16) + E tile (256 x 64 bf16) per k-block into a
+//                4-stage SWIZZLE_128B ring (cp.async.bulk.tensor.2d, mbarrier complete_tx)
+//       warp 1   one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=256, K=16),
+//                fp32 accumulators in TMEM (2 x 256 columns, double-buffered against the epilogue);
+//                tcgen05.commit releases smem stages / publishes accumulators
+//       warps 2-3 per-tile column coefficients (label predicate, row norms) -> smem, one tile ahead
+//       warps 4-7 epilogue: tcgen05.ld 32 columns at a time; thread = query (TMEM lane);
+//                t = fma(s, cA[col], cB[col])  (L2: |e|^2 - 2s  [+|q|^2 is constant per query];
+//                cosine: -s/|e|); pass 1 keeps min t per (query, tile), pass 2 appends the rare
+//                t < thr[q] to a global candidate list
+//   threshold_kernel  k'-th smallest per-tile minimum of a strided sample of tiles = a valid upper
+//                bound of the k'-th smallest t over the whole shard (each such tile holds one
+//                element <= it), tight because the best rows rarely share a tile
+//   select_rerank_kernel  per query: sort the candidates by t, re-score the best k' = 2k from the
+//                fp32 mirror with the same formulas as the single-query scan, sort by the
+//                reference's comparator and emit k records.  Final scores are fp32-exact; bf16 only
+//                decides which k' rows are re-scored.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <float.h>
+
+#include "spl_batch.cuh"
+#include "spl_scan_epilogue.cuh"
+
+namespace spl {
+
+namespace {
+
+constexpr int BM = 128, BN = 256, BK = 64, UK = 16;
+constexpr int kStages = 4, kAcc = 2;
+constexpr int kThreadsGemm = 256;
+constexpr uint32_t kStageA = BM * BK * 2, kStageB = BN * BK * 2, kStageBytes = kStageA + kStageB;
+constexpr uint32_t kTmemCols = 512;
+
+// ---- smem carve-up (dynamic, 1024-byte aligned for SWIZZLE_128B) ----
+struct GemmSmem {
+    static constexpr uint32_t stages_off = 0;
+    static constexpr uint32_t coef_off = kStages * kStageBytes;              // cA[2][BN], cB[2][BN]
+    static constexpr uint32_t bar_off = coef_off + 2 * 2 * BN * 4;
+    static constexpr uint32_t total = bar_off + 256;
+};
+
+__device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bar_init(uint32_t b, uint32_t c) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(b), "r"(c)); }
+__device__ __forceinline__ void bar_arrive(uint32_t b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(b) : "memory"); }
+__device__ __forceinline__ void bar_expect_tx(uint32_t b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint32_t b, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(b), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+// start address >> 4 in [0,14), LBO (ignored for swizzled K-major) = 1 in [16,30), SBO = 1024 B >> 4
+// in [32,46), descriptor version 1 in [46,48), layout type SWIZZLE_128B = 2 in [61,64).
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate (bit 4), A = B = bf16
+// (bits 7, 10), both K-major, N >> 3 at [17,23), M >> 4 at [24,29).
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+}  // namespace
+
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreadsGemm, 1)
+gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapE, const BatchArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ uint32_t s_tmem_base;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bars = s32(smem + GemmSmem::bar_off);
+    // barrier map: full[s] 0..3, empty[s] 4..7, tfull[a] 8..9, tempty[a] 10..11, cfull[c] 12..13, cempty[c] 14..15
+    auto FULL = [&](uint32_t s) { return bars + 8 * s; };
+    auto EMPTY = [&](uint32_t s) { return bars + 8 * (4 + s); };
+    auto TFULL = [&](uint32_t x) { return bars + 8 * (8 + x); };
+    auto TEMPTY = [&](uint32_t x) { return bars + 8 * (10 + x); };
+    auto CFULL = [&](uint32_t x) { return bars + 8 * (12 + x); };
+    auto CEMPTY = [&](uint32_t x) { return bars + 8 * (14 + x); };
+    float *cA = reinterpret_cast<float *>(smem + GemmSmem::coef_off);  // [2][BN]
+    float *cB = cA + 2 * BN;                                          // [2][BN]
+
+    if (threadIdx.x == 0) {
+        for (uint32_t s = 0; s < kStages; s++) { bar_init(FULL(s), 1); bar_init(EMPTY(s), 1); }
+        for (uint32_t x = 0; x < kAcc; x++) {
+            bar_init(TFULL(x), 1); bar_init(TEMPTY(x), 4);
+            bar_init(CFULL(x), 64); bar_init(CEMPTY(x), 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {  // TMEM allocation: one warp, result lands in shared memory
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&s_tmem_base)), "n"(kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = s_tmem_base;
+
+    // ---- static tile schedule: CTA = (query tile, group); groups stride over the tile list ----
+    const uint32_t qtile = blockIdx.x % a.n_qtiles, group = blockIdx.x / a.n_qtiles, ngroups = gridDim.x / a.n_qtiles;
+    const uint32_t kblocks = a.dim / BK;
+    const bool active = group < ngroups;  // CTAs beyond a whole number of groups idle
+
+    if (warp == 0) {
+        if (lane == 0 && active) {
+            uint32_t st = 0, ph = 0;
+            for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
+                const int row0 = (int)((a.tile_first + j * a.tile_stride) * BN);
+                for (uint32_t kb = 0; kb < kblocks; kb++) {
+                    bar_wait(EMPTY(st), ph ^ 1u);
+                    bar_expect_tx(FULL(st), kStageBytes);
+                    const uint32_t sa = s32(smem + st * kStageBytes), sb = sa + kStageA;
+                    tma_load_2d(sa, &mapQ, FULL(st), (int)(kb * BK), (int)(qtile * BM));
+                    tma_load_2d(sb, &mapE, FULL(st), (int)(kb * BK), row0);
+                    if (++st == kStages) { st = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && active) {
+            uint32_t st = 0, ph = 0, acc = 0, aph = 0;
+            for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
+                bar_wait(TEMPTY(acc), aph ^ 1u);
+                tc_fence_after();
+                for (uint32_t kb = 0; kb < kblocks; kb++) {
+                    bar_wait(FULL(st), ph);
+                    tc_fence_after();
+                    const uint32_t sa = s32(smem + st * kStageBytes), sb = sa + kStageA;
+                    const uint64_t da = make_desc(sa), db = make_desc(sb);
+#pragma unroll
+                    for (uint32_t k = 0; k < BK / UK; k++)
+                        tc_mma_f16(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+                    tc_commit(EMPTY(st));  // the stage is free once these MMAs have read it
+                    if (++st == kStages) { st = 0; ph ^= 1u; }
+                }
+                tc_commit(TFULL(acc));     // accumulator complete
+                if (++acc == kAcc) { acc = 0; aph ^= 1u; }
+            }
+        }
+    } else if (warp < 4) {
+        // ---- per-tile column coefficients, one tile ahead of the epilogue ----
+        if (active) {
+            const uint32_t t = threadIdx.x - 64;  // 0..63, four columns each
+            const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+            uint32_t cs = 0, cph = 0;
+            for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
+                const uint32_t row0 = (a.tile_first + j * a.tile_stride) * BN;
+                float va[4], vb[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const uint32_t r = row0 + t + 64 * i;
+                    float ca = 0.f, cb = INFINITY;
+                    if (r < a.n) {
+                        const uint32_t f = a.flags[r];
+                        const bool pass = (f & need) && ((a.bloom[r] & a.mask) == a.mask) && r != a.exclude;
+                        if (pass && (f & SPL_ROW_EMB)) {
+                            const float n2 = a.norm2[r];
+                            if (a.order == SPL_ORDER_L2) { ca = -2.f; cb = n2; }
+                            else { ca = n2 > 0.f ? -rsqrtf(n2) : 0.f; cb = 0.f; }
+                        } else if (pass) {
+                            // no consistent embedding copy: scores like _search.c:388-391 (sim 0, dist FLT_MAX)
+                            ca = 0.f; cb = a.order == SPL_ORDER_L2 ? 3.0e38f : 0.f;
+                        }
+                    }
+                    va[i] = ca; vb[i] = cb;
+                }
+                bar_wait(CEMPTY(cs), cph ^ 1u);
+#pragma unroll
+                for (int i = 0; i < 4; i++) { cA[cs * BN + t + 64 * i] = va[i]; cB[cs * BN + t + 64 * i] = vb[i]; }
+                bar_arrive(CFULL(cs));
+                if (++cs == kAcc) { cs = 0; cph ^= 1u; }
+            }
+        }
+    } else {
+        // ---- epilogue: thread = query (TMEM lane) ----
+        if (active) {
+            const uint32_t quad = warp - 4;                       // TMEM lane quadrant this warp may read
+            const uint32_t ql = quad * 32 + lane;                 // query within the tile
+            const uint32_t q = qtile * BM + ql;
+            const bool qvalid = q < a.nq;
+            const float thr = (a.pass == 2 && qvalid) ? a.thr[q] : -INFINITY;
+            uint32_t acc = 0, aph = 0;
+            for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
+                const uint32_t row0 = (a.tile_first + j * a.tile_stride) * BN;
+                bar_wait(CFULL(acc), aph);
+                bar_wait(TFULL(acc), aph);
+                tc_fence_after();
+                const float *pa = cA + acc * BN, *pb = cB + acc * BN;
+                float tmin = INFINITY;
+#pragma unroll 1
+                for (uint32_t c0 = 0; c0 < BN; c0 += 32) {
+                    uint32_t v[32];
+                    tc_ld32(tmem_base + ((quad * 32u) << 16) + acc * BN + c0, v);
+#pragma unroll
+                    for (int i = 0; i < 32; i++) {
+                        const float t = fmaf(__uint_as_float(v[i]), pa[c0 + i], pb[c0 + i]);
+                        if (a.pass == 1) {
+                            tmin = fminf(tmin, t);
+                        } else if (t < thr) {
+                            const uint32_t pos = atomicAdd(&a.cand_cnt[q], 1u);
+                            if (pos < a.cand_cap) {
+                                a.cand_t[(size_t)q * a.cand_cap + pos] = t;
+                                a.cand_idx[(size_t)q * a.cand_cap + pos] = row0 + c0 + i;
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { bar_arrive(TEMPTY(acc)); bar_arrive(CEMPTY(acc)); }
+                if (a.pass == 1 && qvalid) a.tile_min[(size_t)j * a.nq_pad + q] = tmin;
+                if (++acc == kAcc) { acc = 0; aph ^= 1u; }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// fp32 queries -> bf16 (zero-padded to a multiple of 128 rows) + |bf16(q)|^2
+__global__ void __launch_bounds__(256) qprep_kernel(const float *__restrict__ q, uint32_t nq, uint32_t nq_pad, uint32_t dim,
+                                                    __nv_bfloat16 *__restrict__ q16) {
+    const uint32_t row = blockIdx.x;
+    for (uint32_t d = threadIdx.x; d < dim; d += blockDim.x)
+        q16[(size_t)row * dim + d] = __float2bfloat16_rn(row < nq ? q[(size_t)row * dim + d] : 0.f);
+    (void)nq_pad;
+}
+
+// thr[q] = k'-th smallest tile minimum over the sampled tiles (+inf if fewer than k' finite ones)
+__global__ void __launch_bounds__(256) threshold_kernel(const float *__restrict__ tile_min, uint32_t n_tiles, uint32_t nq,
+                                                        uint32_t nq_pad, uint32_t kprime, float *__restrict__ thr) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
+    const uint32_t q = blockIdx.x;
+    const uint32_t P = next_pow2(n_tiles < 2 ? 2 : n_tiles);
+    uint32_t *idx = reinterpret_cast<uint32_t *>(keys + P);
+    for (uint32_t i = threadIdx.x; i < P; i += blockDim.x) {
+        const float v = i < n_tiles ? tile_min[(size_t)i * nq_pad + q] : INFINITY;
+        keys[i] = f2ord(v); idx[i] = i;
+    }
+    __syncthreads();
+    bitonic_sort_cta(keys, idx, P);
+    if (threadIdx.x == 0) {
+        float t = INFINITY;
+        if (kprime <= n_tiles) t = ord2f((uint32_t)keys[kprime - 1]);
+        // nudge up by one ulp-ish so the bounding element itself passes `t < thr`
+        thr[q] = isfinite(t) ? nextafterf(t, INFINITY) : INFINITY;
+    }
+    (void)nq;
+}
+
+// per query: sort candidates by t, exact fp32 re-score of the best k', reference order, emit k
+__global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, const float *__restrict__ q32, uint32_t k,
+                                                           uint32_t kprime, spl_gpu_result *__restrict__ out,
+                                                           uint32_t out_stride, uint32_t *__restrict__ out_count,
+                                                           uint32_t *__restrict__ overflow) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t total = a.cand_cnt[q];
+    if (total > a.cand_cap) {  // threshold too loose for this query: the host re-runs it on the fp32 scan
+        if (threadIdx.x == 0) { overflow[q] = 1; out_count[q] = 0; }
+        return;
+    }
+    const uint32_t P = next_pow2(total < 2 ? 2 : total);
+    uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
+    uint32_t *idx = reinterpret_cast<uint32_t *>(keys + P);
+    for (uint32_t i = threadIdx.x; i < P; i += blockDim.x) {
+        uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
+        if (i < total) { key = f2ord(a.cand_t[(size_t)q * a.cand_cap + i]); id = a.cand_idx[(size_t)q * a.cand_cap + i]; }
+        keys[i] = key; idx[i] = id;
+    }
+    __syncthreads();
+    bitonic_sort_cta(keys, idx, P);
+    const uint32_t m = total < kprime ? total : kprime;   // candidates to re-score
+    __shared__ uint64_t rk[512];
+    __shared__ uint32_t ri[512];
+    const uint32_t R = next_pow2(m < 2 ? 2 : m);
+    for (uint32_t i = threadIdx.x; i < R; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = kIdxSentinel; }
+    __syncthreads();
+    // |q|^2 (fp32) once per warp
+    const float *qv = q32 + (size_t)q * a.dim;
+    float ma = 0.f;
+    for (uint32_t d = lane; d < a.dim; d += 32) ma = fmaf(qv[d], qv[d], ma);
+    ma = warp_sum(ma);
+    for (uint32_t c = warp; c < m; c += blockDim.x / 32) {
+        const uint32_t row = idx[c];
+        const float *e = a.E + (size_t)row * a.dim;
+        float dot = 0.f, mb = 0.f, ss = 0.f;
+        for (uint32_t d = lane; d < a.dim; d += 32) {
+            const float x = e[d], y = qv[d], t = y - x;
+            dot = fmaf(y, x, dot); mb = fmaf(x, x, mb); ss = fmaf(t, t, ss);
+        }
+        dot = warp_sum(dot); mb = warp_sum(mb); ss = warp_sum(ss);
+        float sim = cosine_from_sums(dot, ma, mb), dist = __fsqrt_rn(ss);
+        if (!(a.flags[row] & SPL_ROW_EMB)) { sim = 0.f; dist = FLT_MAX; }
+        if (lane == 0) { rk[c] = make_key(a.order, sim, dist); ri[c] = row; }
+    }
+    __syncthreads();
+    bitonic_sort_cta(rk, ri, R);
+    const uint32_t nout = m < k ? m : k;
+    for (uint32_t t = threadIdx.x; t < nout; t += blockDim.x) {
+        spl_gpu_result r;
+        split_key(a.order, rk[t], r.similarity, r.distance);
+        const uint32_t row = ri[t];
+        r.slot_idx = (uint32_t)(a.row0 + row);
+        r.has_embedding = (a.flags[row] & SPL_ROW_EMB) ? 1u : 0u;
+        r.epoch = a.epoch[row];
+        r.bloom = a.bloom[row];
+        out[(size_t)q * out_stride + t] = r;
+    }
+    if (threadIdx.x == 0) out_count[q] = nout;
+}
+
+// -------------------------------------------------------------------------------------------------
+// host side
+// -------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D bf16 row-major [rows][dim] tensor, box = {64 elements (128 B), box_rows}, 128-byte swizzle
+static bool make_map(CUtensorMap *map, const void *base, uint64_t rows, uint32_t dim, uint32_t box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    cuuint64_t gdim[2] = { dim, rows };
+    cuuint64_t gstride[1] = { (cuuint64_t)dim * 2 };
+    cuuint32_t box[2] = { (cuuint32_t)BK, box_rows };
+    cuuint32_t estr[2] = { 1, 1 };
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+cudaError_t batch_prepare() {
+    return cudaFuncSetAttribute(gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmem::total);
+}
+
+bool batch_supported(uint32_t dim, uint32_t k) { return dim % BK == 0 && dim >= BK && k >= 1 && k <= 128; }
+
+size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, BatchScratchLayout *L) {
+    const uint32_t nq_pad = (nq_max + BM - 1) / BM * BM;
+    const uint32_t tiles = (n_rows + BN - 1) / BN;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    L->q16_off = take((size_t)nq_pad * dim * 2);
+    L->thr_off = take((size_t)nq_pad * 4);
+    L->cnt_off = take((size_t)nq_pad * 4);
+    L->ovf_off = take((size_t)nq_pad * 4);
+    L->tile_min_off = take((size_t)tiles * nq_pad * 4);
+    L->cand_t_off = take((size_t)nq_pad * kBatchCandCap * 4);
+    L->cand_idx_off = take((size_t)nq_pad * kBatchCandCap * 4);
+    L->nq_pad = nq_pad;
+    return off;
+}
+
+cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, unsigned char *scratch, const float *d_q32,
+                         uint32_t k, int sm_count, spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts,
+                         uint32_t **d_overflow_out, uint32_t *launches, cudaStream_t s) {
+    BatchArgs a = base;
+    a.nq_pad = (a.nq + BM - 1) / BM * BM;
+    a.n_qtiles = a.nq_pad / BM;
+    __nv_bfloat16 *q16 = reinterpret_cast<__nv_bfloat16 *>(scratch + L.q16_off);
+    a.thr = reinterpret_cast<float *>(scratch + L.thr_off);
+    a.cand_cnt = reinterpret_cast<uint32_t *>(scratch + L.cnt_off);
+    uint32_t *overflow = reinterpret_cast<uint32_t *>(scratch + L.ovf_off);
+    a.tile_min = reinterpret_cast<float *>(scratch + L.tile_min_off);
+    a.cand_t = reinterpret_cast<float *>(scratch + L.cand_t_off);
+    a.cand_idx = reinterpret_cast<uint32_t *>(scratch + L.cand_idx_off);
+    a.cand_cap = kBatchCandCap;
+    *d_overflow_out = overflow;
+    const uint32_t kprime = 2 * k;
+
+    CUtensorMap mapQ, mapE;
+    if (!make_map(&mapQ, q16, a.nq_pad, a.dim, BM) || !make_map(&mapE, a.E16, a.n, a.dim, BN)) return cudaErrorNotSupported;
+
+    cudaError_t e;
+    qprep_kernel<<<a.nq_pad, 256, 0, s>>>(d_q32, a.nq, a.nq_pad, a.dim, q16);
+    if ((e = cudaGetLastError())) return e;
+    if ((e = cudaMemsetAsync(a.cand_cnt, 0, (size_t)a.nq_pad * 4, s))) return e;
+    if ((e = cudaMemsetAsync(overflow, 0, (size_t)a.nq_pad * 4, s))) return e;
+
+    const uint32_t tiles = (a.n + BN - 1) / BN;
+    int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;
+    if (grid < (int)a.n_qtiles) grid = (int)a.n_qtiles;
+    // pass 1: a strided sample of tiles (every tile when the shard is small) -> per-tile minima -> thresholds
+    // expected survivors of pass 2 ~ stride * k' (the k'-th smallest of a 1/stride sample)
+    uint32_t stride = 1024u / kprime;
+    if (stride > 16) stride = 16;
+    while (stride > 1 && (tiles + stride - 1) / stride < 4 * kprime) stride >>= 1;
+    if (stride < 1) stride = 1;
+    const uint32_t sampled = (tiles + stride - 1) / stride;
+    a.pass = 1; a.tile_first = 0; a.tile_stride = stride; a.n_tiles = sampled;
+    gemm_topk_kernel<<<grid, kThreadsGemm, GemmSmem::total, s>>>(mapQ, mapE, a);
+    if ((e = cudaGetLastError())) return e;
+    const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
+    threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, sampled, a.nq, a.nq_pad, kprime, a.thr);
+    if ((e = cudaGetLastError())) return e;
+    // pass 2: every tile, append what beats the threshold
+    a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
+    gemm_topk_kernel<<<grid, kThreadsGemm, GemmSmem::total, s>>>(mapQ, mapE, a);
+    if ((e = cudaGetLastError())) return e;
+    static bool attr = false;
+    const size_t sel_smem = (size_t)kBatchCandCap * 12;
+    if (!attr) {
+        if ((e = cudaFuncSetAttribute(select_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem))) return e;
+        attr = true;
+    }
+    select_rerank_kernel<<<a.nq, 256, sel_smem, s>>>(a, d_q32, k, kprime, d_out, out_stride, d_counts, overflow);
+    if ((e = cudaGetLastError())) return e;
+    *launches = 5;
+    return cudaSuccess;
+}
+
+}  // namespace spl

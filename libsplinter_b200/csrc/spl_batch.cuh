@@ -1,0 +1,52 @@
+// spl_batch.cuh -- argument block + host entry points of the batched tensor-core search (spl_batch.cu)
+#pragma once
+#include <cuda_bf16.h>
+
+#include "spl_device.cuh"
+
+namespace spl {
+
+constexpr uint32_t kBatchCandCap = 4096;  // per-query candidate list capacity (entries)
+constexpr uint32_t kBatchMaxQ = 1024;     // queries per batched launch (larger requests are split)
+
+struct BatchArgs {
+    // mirror
+    const float *E;               // fp32 rows (exact re-score)
+    const __nv_bfloat16 *E16;     // bf16 shadow rows (tensor-core operand)
+    const float *norm2;           // |bf16(e)|^2
+    const uint64_t *bloom;
+    const uint8_t *flags;
+    const uint64_t *epoch;
+    uint32_t n, dim;
+    // request
+    uint32_t nq, nq_pad, n_qtiles, order;
+    uint64_t mask;
+    uint32_t exclude;             // local row or kIdxSentinel
+    uint64_t row0;
+    // schedule
+    uint32_t pass;                // 1: per-tile minima, 2: append below threshold
+    uint32_t tile_first, tile_stride, n_tiles;
+    // scratch
+    float *thr;                   // [nq_pad]
+    float *tile_min;              // [n_tiles][nq_pad]
+    uint32_t *cand_cnt;           // [nq_pad]
+    float *cand_t;                // [nq_pad][cand_cap]
+    uint32_t *cand_idx;           // [nq_pad][cand_cap]
+    uint32_t cand_cap;
+};
+
+struct BatchScratchLayout {
+    size_t q16_off, thr_off, cnt_off, ovf_off, tile_min_off, cand_t_off, cand_idx_off;
+    uint32_t nq_pad;
+};
+
+cudaError_t batch_prepare();  // once per device
+bool batch_supported(uint32_t dim, uint32_t k);
+size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, BatchScratchLayout *L);
+// enqueues: query prep, sampling pass, thresholds, full pass, select + exact re-rank.  d_counts[q] and the
+// flag array returned in *d_overflow_out tell which queries overflowed their candidate list.
+cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, unsigned char *scratch, const float *d_q32,
+                         uint32_t k, int sm_count, spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts,
+                         uint32_t **d_overflow_out, uint32_t *launches, cudaStream_t s);
+
+}  // namespace spl

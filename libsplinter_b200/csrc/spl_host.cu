@@ -26,6 +26,7 @@
 #include <thread>
 #include <vector>
 
+#include "spl_batch.cuh"
 #include "spl_mirror.cuh"
 #include "spl_scan.cuh"
 
@@ -111,6 +112,15 @@ struct spl_gpu_ctx {
     spl_gpu_result *d_big_out = nullptr;
     uint32_t big_out_cap = 0;
     float *d_synth_scale = nullptr;
+    // batched tensor-core path scratch (lazy)
+    unsigned char *d_batch = nullptr;
+    BatchScratchLayout batch_layout{};
+    float *d_qbatch = nullptr;
+    spl_gpu_result *d_bout = nullptr;
+    uint32_t *d_bcount = nullptr;
+    spl_gpu_result *h_bout = nullptr;
+    uint32_t *h_bcount = nullptr;
+    uint32_t bout_cap = 0;
     // bookkeeping
     std::mutex mu;  // serialises enqueueing on `stream` and the scratch above
     std::atomic<uint64_t> launches{0};
@@ -143,6 +153,7 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     CUDA_TRY(cudaEventCreate(&c->ev0));
     CUDA_TRY(cudaEventCreate(&c->ev1));
     CUDA_TRY(scan_tma_prepare());
+    CUDA_TRY(batch_prepare());
     const char *impl = getenv("SPL_GPU_SCAN_IMPL");  // developer knob: "ldg" forces the register-path kernel
     c->force_ldg = impl && strcmp(impl, "ldg") == 0;
     if (getenv("SPL_GPU_DEBUG_TIMELINE")) {
@@ -223,6 +234,8 @@ static void destroy(spl_gpu_ctx *c) {
     cudaFree(c->m.E); cudaFree(c->m.bloom); cudaFree(c->m.flags); cudaFree(c->m.epoch);
     cudaFree(c->m.E16); cudaFree(c->m.norm2);
     cudaFree(c->d_cands); cudaFree(c->d_counters); cudaFree(c->d_q); cudaFree(c->d_out); cudaFree(c->d_count);
+    cudaFree(c->d_batch); cudaFree(c->d_qbatch); cudaFree(c->d_bout); cudaFree(c->d_bcount);
+    cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount);
     cudaFree(c->d_keys); cudaFree(c->d_sort_tmp); cudaFree(c->d_big_out); cudaFree(c->d_synth_scale);
     cudaFreeHost(c->h_q); cudaFreeHost(c->h_out); cudaFreeHost(c->h_count);
     for (StageBuf &b : c->stage) {
@@ -641,6 +654,7 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
     if (mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "mode %u is not available for this query shape", mode);
     ScanArgs a;
     fill_args(c, p, a);
+    a.k = p->k;
     for (uint32_t qi = 0; qi < p->nq; qi++) {
         a.q = d_q + (size_t)qi * c->dim;
         a.out = d_out + (size_t)qi * out_stride;
@@ -649,6 +663,57 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         else CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
         c->launches++;
     }
+    return 0;
+}
+
+static int ensure_batch_scratch(spl_gpu_ctx *c, uint32_t k) {
+    int rc;
+    if (!c->d_batch) {
+        const size_t bytes = batch_scratch_bytes((uint32_t)c->n, kBatchMaxQ, c->dim, &c->batch_layout);
+        if ((rc = dev_alloc(c, &c->d_batch, bytes, false))) return rc;
+        if ((rc = dev_alloc(c, &c->d_qbatch, (size_t)kBatchMaxQ * c->dim, false))) return rc;
+    }
+    const uint32_t need = kBatchMaxQ * k;
+    if (c->bout_cap < need) {
+        if (c->d_bout) { cudaFree(c->d_bout); cudaFree(c->d_bcount); cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount); }
+        if ((rc = dev_alloc(c, &c->d_bout, need, false))) return rc;
+        if ((rc = dev_alloc(c, &c->d_bcount, 2 * kBatchMaxQ, false))) return rc;
+        CUDA_TRY(cudaMallocHost((void **)&c->h_bout, (size_t)need * sizeof(spl_gpu_result)));
+        CUDA_TRY(cudaMallocHost((void **)&c->h_bcount, (size_t)2 * kBatchMaxQ * sizeof(uint32_t)));
+        c->bout_cap = need;
+    }
+    return 0;
+}
+
+static bool wants_batch(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {
+    if (p->mode == SPL_MODE_BATCH_BF16) return true;
+    return p->mode == SPL_MODE_AUTO && p->nq >= 16 && c->m.E16 && batch_supported(c->dim, p->k) &&
+           !(p->min_similarity > 0.f) && !(p->max_distance > 0.f);
+}
+
+static int check_batch(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {
+    if (!c->m.E16) return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available: attach with SPL_OPT_BF16_MIRROR");
+    if (!batch_supported(c->dim, p->k)) return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available for dim %u / k %u (dim %% 64 == 0, 1 <= k <= 128)", c->dim, p->k);
+    if (p->min_similarity > 0.f || p->max_distance > 0.f)
+        return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available with --similarity / --distance thresholds");
+    return 0;
+}
+
+// enqueue one batched search of nq <= kBatchMaxQ queries (fp32, on the device); caller holds c->mu
+static int enqueue_batch(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, uint32_t nq, spl_gpu_result *d_out,
+                         uint32_t out_stride, uint32_t *d_counts, uint32_t **d_overflow, cudaStream_t s) {
+    BatchArgs b;
+    memset(&b, 0, sizeof b);
+    b.E = c->m.E; b.E16 = c->m.E16; b.norm2 = c->m.norm2; b.bloom = c->m.bloom; b.flags = c->m.flags; b.epoch = c->m.epoch;
+    b.n = (uint32_t)c->n; b.dim = c->dim; b.nq = nq; b.order = p->order; b.mask = p->bloom_mask;
+    b.exclude = kIdxSentinel;
+    if (p->exclude_slot != SPL_NO_SLOT && p->exclude_slot >= c->slot_begin && p->exclude_slot < c->slot_begin + c->n)
+        b.exclude = (uint32_t)(p->exclude_slot - c->slot_begin);
+    b.row0 = c->slot_begin;
+    uint32_t launches = 0;
+    CUDA_TRY(batch_search(b, c->batch_layout, c->d_batch, d_q, p->k, c->sm_count, d_out, out_stride, d_counts, d_overflow,
+                          &launches, s));
+    c->launches += launches;
     return 0;
 }
 
@@ -661,7 +726,16 @@ extern "C" int spl_gpu_search_device(spl_gpu_ctx *c, const spl_gpu_search_params
     if (out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
     cudaSetDevice(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
-    return enqueue_fused(c, p, d_q, d_out, out_stride, d_counts, stream ? (cudaStream_t)stream : c->stream);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    if (wants_batch(c, p)) {
+        if ((rc = check_batch(c, p))) return rc;
+        if (p->nq > kBatchMaxQ) return fail(-2, EINVAL, "device-buffer batched search takes at most %u queries per call", kBatchMaxQ);
+        if ((rc = ensure_batch_scratch(c, p->k))) return rc;
+        uint32_t *ovf = nullptr;
+        // a query whose candidate list overflowed reports count 0 here; the host-buffer call re-runs it exactly
+        return enqueue_batch(c, p, d_q, p->nq, d_out, out_stride, d_counts, &ovf, s);
+    }
+    return enqueue_fused(c, p, d_q, d_out, out_stride, d_counts, s);
 }
 
 static int ensure_sort_scratch(spl_gpu_ctx *c, uint32_t out_cap) {
@@ -692,6 +766,45 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
     std::lock_guard<std::mutex> lk(c->mu);
     const size_t qbytes = (size_t)c->dim * sizeof(float);
     const bool fused = p->k >= 1 && p->k <= SPL_GPU_KMAX_FUSED;
+    if (wants_batch(c, p)) {
+        if ((rc = check_batch(c, p))) return rc;
+        if ((rc = ensure_batch_scratch(c, p->k))) return rc;
+        for (uint32_t q0 = 0; q0 < p->nq; q0 += kBatchMaxQ) {
+            const uint32_t nq = (p->nq - q0 < kBatchMaxQ) ? p->nq - q0 : kBatchMaxQ;
+            CUDA_TRY(cudaMemcpyAsync(c->d_qbatch, q + (size_t)q0 * c->dim, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
+            uint32_t *d_ovf = nullptr;
+            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+            if ((rc = enqueue_batch(c, p, c->d_qbatch, nq, c->d_bout, p->k, c->d_bcount, &d_ovf, c->stream))) return rc;
+            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+            CUDA_TRY(cudaMemcpyAsync(c->h_bout, c->d_bout, (size_t)nq * p->k * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(cudaMemcpyAsync(c->h_bcount, c->d_bcount, nq * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(cudaMemcpyAsync(c->h_bcount + kBatchMaxQ, d_ovf, nq * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            if (c->timing) {
+                float ms = 0.f;
+                CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+                c->last_scan_ms = ms;
+            }
+            for (uint32_t i = 0; i < nq; i++) {
+                if (c->h_bcount[kBatchMaxQ + i]) {
+                    // candidate list overflowed (threshold from the sample was too loose for this query):
+                    // answer it with the fp32 single-query scan instead -- still on the GPU, never on the CPU
+                    spl_gpu_search_params one = *p;
+                    one.nq = 1; one.mode = SPL_MODE_FAST;
+                    memcpy(c->h_q, q + (size_t)(q0 + i) * c->dim, qbytes);
+                    CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, qbytes, cudaMemcpyHostToDevice, c->stream));
+                    if ((rc = enqueue_fused(c, &one, c->d_q, c->m_out, p->k, c->m_count, c->stream))) return rc;
+                    CUDA_TRY(cudaStreamSynchronize(c->stream));
+                    counts[q0 + i] = c->h_count[0];
+                    memcpy(out + (size_t)(q0 + i) * out_stride, c->h_out, (size_t)c->h_count[0] * sizeof(spl_gpu_result));
+                } else {
+                    counts[q0 + i] = c->h_bcount[i];
+                    memcpy(out + (size_t)(q0 + i) * out_stride, c->h_bout + (size_t)i * p->k, (size_t)c->h_bcount[i] * sizeof(spl_gpu_result));
+                }
+            }
+        }
+        return 0;
+    }
     if (fused) {
         // process in chunks of q_cap queries through the pinned staging buffers
         for (uint32_t q0 = 0; q0 < p->nq; q0 += c->q_cap) {

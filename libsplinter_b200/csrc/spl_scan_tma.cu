@@ -265,6 +265,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         uint32_t slot = warp, gen = 0;  // this warp's pair index = gen * NP + slot
         if (slot >= NP) { slot -= NP; gen++; }
         for (;;) {
+            // When the ring size is not a multiple of the consumer count a slot's successive rounds belong to
+            // DIFFERENT warps, and one of them can get here before the previous round has even been filled; a
+            // 1-bit phase would then read as "complete".  The generation word says the previous round is done.
+            wait_gen(empty0 + 8 * slot, gen);
             mbar_wait(full0 + 8 * slot, gen & 1u);
             const uint4 mt = meta[slot];
             if (mt.x == kIdxSentinel) break;

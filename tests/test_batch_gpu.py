@@ -1,0 +1,91 @@
+"""GPU parity tests of the batched tensor-core path (SPL_MODE_BATCH_BF16, config C3) against the fp32
+CPU oracle.  bf16 is used only to pick which 2k rows get re-scored; the scores returned are fp32 and
+must meet the same tolerance as the single-query scan.  The oracle for this config is the restated
+loop over queries (D=1024 / L2 order / batching are not expressible by the shipped CLI)."""
+import numpy as np
+import pytest
+
+import libsplinter_b200 as sg
+import support
+
+pytestmark = pytest.mark.gpu
+
+
+def _mirror(n, dim, row0=0, seed=1234):
+    E, bloom, flags = support.synth_dense(seed, 99, row0, n, dim)
+    m = sg.Mirror.open_dense(n, dim, global_row0=row0, flags=sg.OPT_BF16_MIRROR)
+    m.dense_upload(0, E, bloom, flags)
+    return m, E, bloom, flags
+
+
+def _check(m, E, bloom, flags, q, k, row0=0, **kw):
+    out, counts = m.search(q, k, mode=sg.MODE_BATCH_BF16, **kw)
+    ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=k, order=kw.get("order", sg.ORDER_COSINE),
+                                          bloom_mask=kw.get("bloom_mask", 0))
+    bad = 0
+    for i in range(q.shape[0]):
+        got = out[i][:counts[i]].copy()
+        got["slot_idx"] -= row0
+        assert counts[i] == rc[i]
+        support.assert_topk_matches(got, ref[i][:rc[i]], exact=False, order=kw.get("order", sg.ORDER_COSINE))
+        bad += int(not np.array_equal(got["slot_idx"], ref[i][:rc[i]]["idx"]))
+    return bad
+
+
+@pytest.mark.parametrize("dim", [1024, 768])
+@pytest.mark.parametrize("order", [sg.ORDER_L2, sg.ORDER_COSINE])
+def test_batched_topk_matches_oracle(dim, order):
+    n, nq, k = 70_000, 200, 32       # n, nq deliberately not multiples of the 256 x 128 tile
+    m, E, bloom, flags = _mirror(n, dim, row0=512)
+    q = support.synth_queries(4321, nq, dim)
+    try:
+        _check(m, E, bloom, flags, q, k, row0=512, order=order)
+        _check(m, E, bloom, flags, q[:40], 10, row0=512, order=order, bloom_mask=0x3)
+    finally:
+        m.close()
+
+
+def test_batched_small_shapes_and_auto_mode():
+    dim = 1024
+    m, E, bloom, flags = _mirror(300, dim)   # less than one tile of rows
+    q = support.synth_queries(7, 3, dim)
+    try:
+        _check(m, E, bloom, flags, q, 5, order=sg.ORDER_L2)
+        _check(m, E, bloom, flags, q[:1], 32, order=sg.ORDER_COSINE)
+        # AUTO picks the batched path from 16 queries up when a bf16 mirror exists
+        q16 = support.synth_queries(8, 20, dim)
+        out, counts = m.search(q16, 10)
+        ref, rc = support.oracle_search_dense(q16, E, bloom, flags, k=10)
+        for i in range(20):
+            support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
+    finally:
+        m.close()
+
+
+def test_batched_overflow_falls_back_to_the_fp32_scan():
+    """Adversarial corpus: 20 000 exact duplicates tie on every ordering value, so every row beats the
+    sampled threshold, the candidate list overflows, and the affected queries are answered by the fp32
+    scan instead -- same results (ties broken by ascending slot index), never a CPU fallback."""
+    n, dim = 20_000, 1024
+    rng = np.random.default_rng(3)
+    base = rng.standard_normal(dim).astype(np.float32)
+    E = np.tile(base, (n, 1))
+    E[5000] = base * 0.5          # a few distinct rows
+    E[17] = -base
+    bloom = np.zeros(n, np.uint64)
+    flags = np.full(n, 7, np.uint8)
+    q = (base[None, :] + rng.standard_normal((4, dim)).astype(np.float32) * 0.5).astype(np.float32)
+    with sg.Mirror.open_dense(n, dim, flags=sg.OPT_BF16_MIRROR) as m:
+        m.dense_upload(0, E, bloom, flags)
+        for order in (sg.ORDER_L2, sg.ORDER_COSINE):
+            out, counts = m.search(q, 16, mode=sg.MODE_BATCH_BF16, order=order)
+            ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=16, order=order)
+            for i in range(4):
+                support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]], order=order)
+                assert 17 not in out[i]["slot_idx"][:counts[i]]
+
+
+def test_batched_mode_needs_the_bf16_mirror():
+    with sg.Mirror.open_dense(1000, 1024) as m:
+        with pytest.raises(sg.SplinterGpuError, match="not available"):
+            m.search(np.zeros((4, 1024), np.float32), 10, mode=sg.MODE_BATCH_BF16)

@@ -163,3 +163,21 @@ def test_bad_arguments_fail_loudly(corpus):
     rc = sg.load().spl_gpu_search(m.handle, C.byref(p), q.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p),
                                   10, cnt.ctypes.data_as(C.c_void_p))
     assert rc == -2
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("dim,k", [(1024, 10), (1024, 32), (768, 256), (512, 100)])
+def test_rings_whose_slots_rotate_between_consumer_warps(mode, dim, k):
+    """Regression: when the shared-memory ring size is not a multiple of the consumer-warp count a slot's
+    successive rounds are drained by different warps; an early warp once mistook the 1-bit mbarrier phase
+    of the PREVIOUS round for its own (hang / fault on dense dim=1024 scans).  Dense, repeated."""
+    n = 30_000
+    E, bloom, flags = support.synth_dense(77, 78, 0, n, dim)
+    q = support.synth_queries(79, 6, dim)
+    with sg.Mirror.open_dense(n, dim) as m:
+        m.dense_upload(0, E, bloom, flags)
+        ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=k)
+        for rep in range(4):
+            out, counts = m.search(q, k, mode=mode)
+            for i in range(q.shape[0]):
+                support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]], exact=(mode == sg.MODE_EXACT))
