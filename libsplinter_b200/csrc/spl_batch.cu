@@ -219,7 +219,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
             const uint32_t ql = quad * 32 + lane;                 // query within the tile
             const uint32_t q = qtile * BM + ql;
             const bool qvalid = q < a.nq;
+            // composite bound (t, row): ties on t -- e.g. thousands of never-embedded zero rows -- are cut by row index
             const float thr = (a.pass == 2 && qvalid) ? a.thr[q] : -INFINITY;
+            const uint32_t thr_row = (a.pass == 2 && qvalid) ? a.thr_row[q] : 0u;
             uint32_t acc = 0, aph = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 const uint32_t row0 = (a.tile_first + j * a.tile_stride) * BN;
@@ -228,6 +230,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 tc_fence_after();
                 const float *pa = cA + acc * BN, *pb = cB + acc * BN;
                 float tmin = INFINITY;
+                uint32_t imin = kIdxSentinel;
 #pragma unroll 1
                 for (uint32_t c0 = 0; c0 < BN; c0 += 32) {
                     uint32_t v[32];
@@ -236,8 +239,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                     for (int i = 0; i < 32; i++) {
                         const float t = fmaf(__uint_as_float(v[i]), pa[c0 + i], pb[c0 + i]);
                         if (a.pass == 1) {
-                            tmin = fminf(tmin, t);
-                        } else if (t < thr) {
+                            if (t < tmin) { tmin = t; imin = row0 + c0 + i; }  // first (lowest) row of the minimum
+                        } else if (t <= thr && (t < thr || row0 + c0 + i <= thr_row)) {
                             const uint32_t pos = atomicAdd(&a.cand_cnt[q], 1u);
                             if (pos < a.cand_cap) {
                                 a.cand_t[(size_t)q * a.cand_cap + pos] = t;
@@ -249,7 +252,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) { bar_arrive(TEMPTY(acc)); bar_arrive(CEMPTY(acc)); }
-                if (a.pass == 1 && qvalid) a.tile_min[(size_t)j * a.nq_pad + q] = tmin;
+                if (a.pass == 1 && qvalid) {
+                    a.tile_min[(size_t)j * a.nq_pad + q] = tmin;
+                    a.tile_min_row[(size_t)j * a.nq_pad + q] = imin;
+                }
                 if (++acc == kAcc) { acc = 0; aph ^= 1u; }
             }
         }
@@ -273,8 +279,9 @@ __global__ void __launch_bounds__(256) qprep_kernel(const float *__restrict__ q,
 }
 
 // thr[q] = k'-th smallest tile minimum over the sampled tiles (+inf if fewer than k' finite ones)
-__global__ void __launch_bounds__(256) threshold_kernel(const float *__restrict__ tile_min, uint32_t n_tiles, uint32_t nq,
-                                                        uint32_t nq_pad, uint32_t kprime, float *__restrict__ thr) {
+__global__ void __launch_bounds__(256) threshold_kernel(const float *__restrict__ tile_min, const uint32_t *__restrict__ tile_min_row,
+                                                        uint32_t n_tiles, uint32_t nq, uint32_t nq_pad, uint32_t kprime,
+                                                        float *__restrict__ thr, uint32_t *__restrict__ thr_row) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
     const uint32_t q = blockIdx.x;
@@ -282,15 +289,16 @@ __global__ void __launch_bounds__(256) threshold_kernel(const float *__restrict_
     uint32_t *idx = reinterpret_cast<uint32_t *>(keys + P);
     for (uint32_t i = threadIdx.x; i < P; i += blockDim.x) {
         const float v = i < n_tiles ? tile_min[(size_t)i * nq_pad + q] : INFINITY;
-        keys[i] = f2ord(v); idx[i] = i;
+        keys[i] = f2ord(v); idx[i] = i < n_tiles ? tile_min_row[(size_t)i * nq_pad + q] : kIdxSentinel;
     }
     __syncthreads();
     bitonic_sort_cta(keys, idx, P);
     if (threadIdx.x == 0) {
-        float t = INFINITY;
-        if (kprime <= n_tiles) t = ord2f((uint32_t)keys[kprime - 1]);
-        // nudge up by one ulp-ish so the bounding element itself passes `t < thr`
-        thr[q] = isfinite(t) ? nextafterf(t, INFINITY) : INFINITY;
+        // the k'-th smallest (t, row) pair bounds the k' best pairs of the whole shard from above
+        float t = INFINITY; uint32_t r = kIdxSentinel;
+        if (kprime <= n_tiles) { t = ord2f((uint32_t)keys[kprime - 1]); r = idx[kprime - 1]; }
+        if (!(t < INFINITY)) r = kIdxSentinel;
+        thr[q] = t; thr_row[q] = r;
     }
     (void)nq;
 }
@@ -402,9 +410,11 @@ size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, Batch
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     L->q16_off = take((size_t)nq_pad * dim * 2);
     L->thr_off = take((size_t)nq_pad * 4);
+    L->thr_row_off = take((size_t)nq_pad * 4);
     L->cnt_off = take((size_t)nq_pad * 4);
     L->ovf_off = take((size_t)nq_pad * 4);
     L->tile_min_off = take((size_t)tiles * nq_pad * 4);
+    L->tile_min_row_off = take((size_t)tiles * nq_pad * 4);
     L->cand_t_off = take((size_t)nq_pad * kBatchCandCap * 4);
     L->cand_idx_off = take((size_t)nq_pad * kBatchCandCap * 4);
     L->nq_pad = nq_pad;
@@ -419,6 +429,8 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     a.n_qtiles = a.nq_pad / BM;
     __nv_bfloat16 *q16 = reinterpret_cast<__nv_bfloat16 *>(scratch + L.q16_off);
     a.thr = reinterpret_cast<float *>(scratch + L.thr_off);
+    a.thr_row = reinterpret_cast<uint32_t *>(scratch + L.thr_row_off);
+    a.tile_min_row = reinterpret_cast<uint32_t *>(scratch + L.tile_min_row_off);
     a.cand_cnt = reinterpret_cast<uint32_t *>(scratch + L.cnt_off);
     uint32_t *overflow = reinterpret_cast<uint32_t *>(scratch + L.ovf_off);
     a.tile_min = reinterpret_cast<float *>(scratch + L.tile_min_off);
@@ -440,18 +452,20 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     const uint32_t tiles = (a.n + BN - 1) / BN;
     int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;
     if (grid < (int)a.n_qtiles) grid = (int)a.n_qtiles;
-    // pass 1: a strided sample of tiles (every tile when the shard is small) -> per-tile minima -> thresholds
-    // expected survivors of pass 2 ~ stride * k' (the k'-th smallest of a 1/stride sample)
-    uint32_t stride = 1024u / kprime;
-    if (stride > 16) stride = 16;
-    while (stride > 1 && (tiles + stride - 1) / stride < 4 * kprime) stride >>= 1;
-    if (stride < 1) stride = 1;
-    const uint32_t sampled = (tiles + stride - 1) / stride;
-    a.pass = 1; a.tile_first = 0; a.tile_stride = stride; a.n_tiles = sampled;
+    // pass 1: a PREFIX of the tiles (all of them when the shard is small) -> per-tile minima -> thresholds.
+    // With a 1/f sample the expected survivors of pass 2 are ~ f * k'; a prefix (not a strided sample) keeps
+    // that true for ties on t as well, because the bound is the pair (t, row).
+    uint32_t frac = 1024u / kprime;
+    if (frac > 16) frac = 16;
+    uint32_t sampled = tiles / (frac ? frac : 1);
+    if (sampled < 4 * kprime) sampled = 4 * kprime;
+    if (sampled > tiles) sampled = tiles;
+    a.pass = 1; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = sampled;
     gemm_topk_kernel<<<grid, kThreadsGemm, GemmSmem::total, s>>>(mapQ, mapE, a);
     if ((e = cudaGetLastError())) return e;
     const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
-    threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, sampled, a.nq, a.nq_pad, kprime, a.thr);
+    threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, kprime, a.thr,
+                                                       a.thr_row);
     if ((e = cudaGetLastError())) return e;
     // pass 2: every tile, append what beats the threshold
     a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;

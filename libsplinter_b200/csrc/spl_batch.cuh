@@ -27,8 +27,10 @@ struct BatchArgs {
     uint32_t pass;                // 1: per-tile minima, 2: append below threshold
     uint32_t tile_first, tile_stride, n_tiles;
     // scratch
-    float *thr;                   // [nq_pad]
+    float *thr;                   // [nq_pad]   bound on t ...
+    uint32_t *thr_row;            // [nq_pad]   ... and, for ties on t, on the row index
     float *tile_min;              // [n_tiles][nq_pad]
+    uint32_t *tile_min_row;       // [n_tiles][nq_pad]
     uint32_t *cand_cnt;           // [nq_pad]
     float *cand_t;                // [nq_pad][cand_cap]
     uint32_t *cand_idx;           // [nq_pad][cand_cap]
@@ -36,7 +38,7 @@ struct BatchArgs {
 };
 
 struct BatchScratchLayout {
-    size_t q16_off, thr_off, cnt_off, ovf_off, tile_min_off, cand_t_off, cand_idx_off;
+    size_t q16_off, thr_off, thr_row_off, cnt_off, ovf_off, tile_min_off, tile_min_row_off, cand_t_off, cand_idx_off;
     uint32_t nq_pad;
 };
 
