@@ -151,8 +151,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                     bar_wait(EMPTY(st), ph ^ 1u);
                     bar_expect_tx(FULL(st), kStageBytes);
                     const uint32_t sa = s32(smem + st * kStageBytes), sb = sa + kStageA;
-                    tma_load_2d(sa, &mapQ, FULL(st), (int)(kb * BK), (int)(qtile * BM));
-                    tma_load_2d(sb, &mapE, FULL(st), (int)(kb * BK), row0);
+                    // both operands are stored tiled ([tile][k-block][rows][64]): each stage is one contiguous burst
+                    tma_load_2d(sa, &mapQ, FULL(st), 0, (int)((qtile * kblocks + kb) * BM));
+                    tma_load_2d(sb, &mapE, FULL(st), 0, (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN));
                     if (++st == kStages) { st = 0; ph ^= 1u; }
                 }
             }
@@ -273,8 +274,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
 __global__ void __launch_bounds__(256) qprep_kernel(const float *__restrict__ q, uint32_t nq, uint32_t nq_pad, uint32_t dim,
                                                     __nv_bfloat16 *__restrict__ q16) {
     const uint32_t row = blockIdx.x;
+    // tiled like the corpus shadow: [query tile of 128][k-block][128][64]
+    const uint32_t qt = row / BM, rr = row % BM, kblocks = dim / BK;
     for (uint32_t d = threadIdx.x; d < dim; d += blockDim.x)
-        q16[(size_t)row * dim + d] = __float2bfloat16_rn(row < nq ? q[(size_t)row * dim + d] : 0.f);
+        q16[(((size_t)qt * kblocks + d / BK) * BM + rr) * BK + d % BK] = __float2bfloat16_rn(row < nq ? q[(size_t)row * dim + d] : 0.f);
     (void)nq_pad;
 }
 
@@ -384,12 +387,13 @@ static EncodeTiledFn get_encode() {
     return fn;
 }
 
-// 2-D bf16 row-major [rows][dim] tensor, box = {64 elements (128 B), box_rows}, 128-byte swizzle
+// tiled bf16 operand seen as a 2-D [rows * k-blocks][64] tensor (row pitch 128 B, fully contiguous),
+// box = {64 elements (128 B), box_rows}, 128-byte swizzle
 static bool make_map(CUtensorMap *map, const void *base, uint64_t rows, uint32_t dim, uint32_t box_rows) {
     EncodeTiledFn enc = get_encode();
     if (!enc) return false;
-    cuuint64_t gdim[2] = { dim, rows };
-    cuuint64_t gstride[1] = { (cuuint64_t)dim * 2 };
+    cuuint64_t gdim[2] = { (cuuint64_t)BK, rows * (dim / BK) };
+    cuuint64_t gstride[1] = { (cuuint64_t)BK * 2 };
     cuuint32_t box[2] = { (cuuint32_t)BK, box_rows };
     cuuint32_t estr[2] = { 1, 1 };
     return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
@@ -441,7 +445,8 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     const uint32_t kprime = 2 * k;
 
     CUtensorMap mapQ, mapE;
-    if (!make_map(&mapQ, q16, a.nq_pad, a.dim, BM) || !make_map(&mapE, a.E16, a.n, a.dim, BN)) return cudaErrorNotSupported;
+    const uint64_t n_pad = ((uint64_t)a.n + BN - 1) / BN * BN;
+    if (!make_map(&mapQ, q16, a.nq_pad, a.dim, BM) || !make_map(&mapE, a.E16, n_pad, a.dim, BN)) return cudaErrorNotSupported;
 
     cudaError_t e;
     qprep_kernel<<<a.nq_pad, 256, 0, s>>>(d_q32, a.nq, a.nq_pad, a.dim, q16);

@@ -180,8 +180,8 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     if ((rc = dev_alloc(c, &c->m.bloom, c->n, true))) return rc;
     if ((rc = dev_alloc(c, &c->m.flags, c->n, true))) return rc;
     if ((rc = dev_alloc(c, &c->m.epoch, c->n, true))) return rc;
-    if (bf16) {
-        if ((rc = dev_alloc(c, &c->m.E16, c->n * c->dim, true))) return rc;
+    if (bf16 && c->dim % kE16TileK == 0) {  // the tiled bf16 shadow needs whole 64-element k-blocks
+        if ((rc = dev_alloc(c, &c->m.E16, e16_padded_rows(c->n) * c->dim, true))) return rc;
         if ((rc = dev_alloc(c, &c->m.norm2, c->n, true))) return rc;
     }
     c->m.dim = c->dim;

@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(MirrorPtrs m, const f
                 uint2 packed;
                 packed.x = *reinterpret_cast<uint32_t *>(&lo);
                 packed.y = *reinterpret_cast<uint32_t *>(&hi);
-                reinterpret_cast<uint2 *>(m.E16 + (size_t)mt.idx * m.dim)[c] = packed;
+                *reinterpret_cast<uint2 *>(m.E16 + e16_offset(mt.idx, c * 4, m.dim)) = packed;
                 const float2 a = __bfloat1622float2(lo), b = __bfloat1622float2(hi);
                 n2 += a.x * a.x + a.y * a.y + b.x * b.x + b.y * b.y;
             }
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(256) synth_fill_kernel(MirrorPtrs m, uint64_t 
             m.E[(size_t)r * m.dim + d] = v;
             if (m.E16) {
                 const __nv_bfloat16 hb = __float2bfloat16_rn(v);
-                m.E16[(size_t)r * m.dim + d] = hb;
+                m.E16[e16_offset(r, d, m.dim)] = hb;
                 const float fb = __bfloat162float(hb);
                 n2 += fb * fb;
             }

@@ -8,12 +8,23 @@
 
 namespace spl {
 
+// The bf16 shadow is stored TILED for the tensor-core path: [row tile of 256][k-block of 64][256 rows][64
+// elements], so the operand tile one MMA stage needs (256 rows x 64 elements = 32 KB) is ONE contiguous
+// burst in HBM instead of 256 separate 128-byte pieces 2*dim bytes apart.
+constexpr uint32_t kE16TileRows = 256, kE16TileK = 64;
+__host__ __device__ inline size_t e16_offset(uint64_t row, uint32_t k, uint32_t dim) {
+    const uint64_t tile = row / kE16TileRows, rr = row % kE16TileRows;
+    const uint32_t kb = k / kE16TileK, kk = k % kE16TileK;
+    return (((tile * (dim / kE16TileK) + kb) * kE16TileRows + rr) * kE16TileK) + kk;
+}
+__host__ __device__ inline uint64_t e16_padded_rows(uint64_t n) { return (n + kE16TileRows - 1) / kE16TileRows * kE16TileRows; }
+
 struct MirrorPtrs {
     float *E;
     uint64_t *bloom;
     uint8_t *flags;
     uint64_t *epoch;
-    __nv_bfloat16 *E16;  // nullable
+    __nv_bfloat16 *E16;  // nullable; tiled layout, see e16_offset()
     float *norm2;        // nullable
     uint32_t dim;
 };
