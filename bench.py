@@ -223,8 +223,8 @@ def run_ours(args):
     single = world == 1
     total_rows = C2_ROWS if single else C4_ROWS
     k = C2_K if single else C4_K
-    rows = total_rows // world
-    row0 = rank * rows
+    from libsplinter_b200.sharding import shard_range
+    row0, rows = shard_range(total_rows, world, rank)
     peak, peak_src = measured_peaks()
 
     m = sg.Mirror.open_dense(rows, DIM, global_row0=row0, device=local_rank)
@@ -235,7 +235,7 @@ def run_ours(args):
     q_dev = torch.from_numpy(q_host).to(dev)
     out_dev = torch.zeros((k, 32), dtype=torch.uint8, device=dev)
     cnt_dev = torch.zeros(1, dtype=torch.int32, device=dev)
-    gathered = torch.zeros((world, k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
+    gathered = torch.zeros((world * k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
     gcnt = torch.zeros(world, dtype=torch.int32, device=dev) if world > 1 else None
     fin_dev = torch.zeros((k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
     fcnt_dev = torch.zeros(1, dtype=torch.int32, device=dev) if world > 1 else None

@@ -1,0 +1,90 @@
+"""world_size-2 (and 3) CPU tests of the multi-GPU plumbing over gloo: slot-range shards, all-gather of
+the per-rank top-k record lists, k-way merge = the single-store result.  The per-rank search here is the
+CPU oracle (no GPU in this container); on the GPU box bench.py drives the same plumbing with NCCL."""
+import os
+import socket
+import subprocess
+import sys
+import textwrap
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from libsplinter_b200.sharding import shard_range
+
+ROOT = Path(__file__).resolve().parent.parent
+
+WORKER = textwrap.dedent("""
+    import os, sys
+    import numpy as np, torch, torch.distributed as dist
+    sys.path.insert(0, {root!r}); sys.path.insert(0, {root!r} + "/tests")
+    import support
+    from libsplinter_b200.sharding import shard_range, gather_lists
+    from libsplinter_b200.binding import RESULT_DTYPE
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    N, DIM, K = 10_000, 256, 25
+    lo, cnt = shard_range(N, world, rank)
+    E, bloom, flags = support.synth_dense(1234, 99, lo, cnt, DIM)      # this rank's shard only
+    q = support.synth_queries(4321, 3, DIM)
+    ok = True
+    for order, mask in ((0, 0), (0, 3), (1, 1)):
+        ref_local, rc = support.oracle_search_dense(q, E, bloom, flags, k=K, order=order, bloom_mask=mask)
+        for qi in range(3):
+            rec = np.zeros(K, RESULT_DTYPE)
+            n = int(rc[qi])
+            rec["slot_idx"][:n] = ref_local[qi]["idx"][:n] + lo            # GLOBAL slot indices
+            rec["similarity"][:n] = ref_local[qi]["similarity"][:n]
+            rec["distance"][:n] = ref_local[qi]["distance"][:n]
+            rec["has_embedding"][:n] = 1
+            t = torch.from_numpy(rec.view(np.uint8).reshape(K, 32).copy())
+            g, c = gather_lists(t, torch.tensor([n], dtype=torch.int32), world)
+            lists = g.numpy().reshape(world * K, 32).view(RESULT_DTYPE).reshape(world, K)
+            # merge on every rank with the oracle's k-way merge
+            flat = np.zeros((world, K), support.SPLO_RESULT)
+            for w in range(world):
+                flat[w]["idx"] = lists[w]["slot_idx"]; flat[w]["similarity"] = lists[w]["similarity"]
+                flat[w]["distance"] = lists[w]["distance"]
+            out = np.zeros(K, support.SPLO_RESULT)
+            counts = c.numpy().astype(np.uint32)
+            m = support.oracle().splo_merge_topk(support._p(flat), support._p(counts), world, K, order, K, support._p(out))
+            # the single-store answer
+            Eg, bg, fg = support.synth_dense(1234, 99, 0, N, DIM)
+            full, fc = support.oracle_search_dense(q[qi], Eg, bg, fg, k=K, order=order, bloom_mask=mask)
+            ok &= (m == fc[0]) and np.array_equal(out[:m]["idx"], full[0][:m]["idx"]) \\
+                and np.array_equal(out[:m]["similarity"].view(np.uint32), full[0][:m]["similarity"].view(np.uint32))
+    flag = torch.tensor([1 if ok else 0])
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("SHARDING_OK" if int(flag) == 1 else "SHARDING_MISMATCH")
+    dist.destroy_process_group()
+""")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_search_merges_to_the_single_store_answer(world, tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER.format(root=str(ROOT)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)],
+                       capture_output=True, text=True, timeout=300, env={**os.environ, "OMP_NUM_THREADS": "1"})
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "SHARDING_OK" in r.stdout, r.stdout[-500:] + r.stderr[-500:]
+
+
+def test_shard_ranges_cover_the_slot_space_exactly():
+    for total in (1, 7, 4096, 1 << 20, (1 << 26) + 5):
+        for world in (1, 2, 3, 4, 8):
+            seen = 0
+            for r in range(world):
+                lo, cnt = shard_range(total, world, r)
+                assert lo == min(seen, total) or cnt == 0
+                seen += cnt
+            assert seen == total
