@@ -101,7 +101,8 @@ typedef struct spl_gpu_sync_stats {
     uint64_t rows_uploaded;  /* embedding rows re-sent (dirty {hash,epoch} or first sync) */
     uint64_t meta_updated;   /* bloom / validity-only updates (set_label moves no slot epoch) */
     uint64_t skipped_busy;   /* odd epoch or torn copy: previous mirror row kept, retried next sync */
-    uint64_t aba_rechecked;  /* epoch-4 rows re-validated by content after retrain's backward epoch */
+    uint64_t aba_rechecked;  /* rows whose {hash, epoch} were unchanged but whose content fingerprint moved
+                                (retrain's backward epoch makes the epoch alone an unreliable witness) */
     uint64_t bytes_h2d;
     double   sweep_ms, upload_ms;
     uint64_t header_epoch;   /* H->epoch observed at the start of the sweep */

@@ -89,6 +89,7 @@ struct spl_gpu_ctx {
     std::vector<uint64_t> c_hash, c_epoch, c_bloom;
     std::vector<uint8_t> c_flags;   // SPL_ROW_* incl. EMB
     std::vector<uint8_t> c_state;   // bit0: mirrored at least once, bit1: mirrored row is non-zero
+    std::vector<uint64_t> c_fp;     // fingerprint of the mirrored row's first 64 bytes (epoch-ABA detector)
     uint64_t c_header_epoch = 0;
     bool first_sync = true;
     std::atomic<uint64_t> generation{0};
@@ -282,7 +283,7 @@ static spl_gpu_ctx *attach_common(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     c->sync_threads = o ? o->sync_threads : 0;
     if (device_setup(c, o) || alloc_mirror(c, o && (o->flags & SPL_OPT_BF16_MIRROR))) { destroy(c); return nullptr; }
     c->c_hash.assign(c->n, 0); c->c_epoch.assign(c->n, 0); c->c_bloom.assign(c->n, 0);
-    c->c_flags.assign(c->n, 0); c->c_state.assign(c->n, 0);
+    c->c_flags.assign(c->n, 0); c->c_state.assign(c->n, 0); c->c_fp.assign(c->n, 0);
     if (spl_gpu_sync(c, nullptr) != 0) { destroy(c); return nullptr; }
     return c;
 }
@@ -417,6 +418,14 @@ static inline uint8_t validity_bits(uint64_t hash, uint64_t epoch, uint32_t val_
     return f;
 }
 
+// 64-bit fingerprint of the first cache line of an embedding (16 floats)
+static inline uint64_t row_fingerprint(const uint8_t *p) {
+    const uint64_t *w = reinterpret_cast<const uint64_t *>(p);
+    uint64_t h = 0x9E3779B97F4A7C15ull;
+    for (int i = 0; i < 8; i++) { h ^= w[i]; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 29; }
+    return h;
+}
+
 static bool row_is_zero(const uint8_t *p, size_t bytes) {
     const uint64_t *w = reinterpret_cast<const uint64_t *>(p);
     uint64_t acc = 0;
@@ -443,11 +452,12 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, 
             c->c_state[r] = 1;
             continue;
         }
-        if (!row_dirty && header_moved && e1 == 4 && (st & 2)) {
-            // retrain ABA (splinter.c:807-825): the epoch is forced to 4, which is also where a
-            // set + set_embedding slot naturally sits.  A scrubbed row is all-zero: probe it.
-            const uint64_t probe0 = *reinterpret_cast<const uint64_t *>(sl + S_EMBED);
-            if (probe0 == 0 && row_is_zero(sl + S_EMBED, row_bytes)) { row_dirty = true; sc.aba++; }
+        if (!row_dirty && header_moved && h != 0) {
+            // Epoch ABA: splinter_retrain_slot forces the epoch to 4 from anywhere (splinter.c:807-825) and
+            // later writes walk it up again, so an unchanged {hash, epoch} does NOT prove an unchanged row
+            // once H->epoch has moved.  Compare a fingerprint of the row's first cache line (it sits right
+            // behind the metadata line this sweep reads anyway); a scrub or a re-embedding changes it.
+            if (row_fingerprint(sl + S_EMBED) != c->c_fp[r]) { row_dirty = true; sc.aba++; }
         }
         if (!row_dirty) {
             // label changes move no slot epoch (splinter.c:843): compare bloom + validity bits
@@ -482,6 +492,12 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, 
             key0 = sl[S_KEY];
             std::atomic_thread_fence(std::memory_order_acquire);
             ok = ld_acq64(sl + S_EPOCH) == es;          // splinter.c:602-603
+            // Hardening beyond the reference's own reader.  The epoch is not monotonic: retrain forces it to 4
+            // from anywhere (splinter.c:807-825) and unset + set restart it, so a reader that is descheduled in
+            // the middle of its copy can come back to the SAME even epoch it started with after any number of
+            // writes (seen under the mixed-workload stress test).  Re-compare the staged bytes with the slot
+            // and re-check the epoch: a write that overlapped the copy changes one or the other.
+            if (ok) ok = memcmp(dst, sl + S_EMBED, row_bytes) == 0 && ld_acq64(sl + S_EPOCH) == es;
         }
         if (!ok) {
             sc.busy++;
@@ -504,6 +520,7 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, 
         b.n++;
         c->c_hash[r] = hh; c->c_epoch[r] = es; c->c_bloom[r] = bloom; c->c_flags[r] = f;
         c->c_state[r] = 1 | (row_is_zero(reinterpret_cast<const uint8_t *>(dst), row_bytes) ? 0 : 2);
+        c->c_fp[r] = row_fingerprint(reinterpret_cast<const uint8_t *>(dst));
         sc.rows++;
         if (b.n == b.cap) {
             if (flush_buf(c, b, true, sc)) { sc.err = 1; return; }
