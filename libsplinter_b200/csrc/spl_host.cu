@@ -27,6 +27,7 @@
 #include <vector>
 
 #include "spl_batch.cuh"
+#include "spl_exact.cuh"
 #include "spl_mirror.cuh"
 #include "spl_scan.cuh"
 
@@ -103,6 +104,8 @@ struct spl_gpu_ctx {
     float *d_q = nullptr, *h_q = nullptr;
     spl_gpu_result *d_out = nullptr, *h_out = nullptr;
     uint32_t *d_count = nullptr, *h_count = nullptr;
+    spl_gpu_result h_bounce[SPL_GPU_KMAX_FUSED];  // small host bounce buffers for the retry paths
+    uint32_t h_bounce_count = 0;
     spl_gpu_result *m_out = nullptr;  // device views of the mapped host buffers h_out / h_count
     uint32_t *m_count = nullptr;
     uint32_t q_cap = 0, out_cap = 0;
@@ -113,6 +116,9 @@ struct spl_gpu_ctx {
     spl_gpu_result *d_big_out = nullptr;
     uint32_t big_out_cap = 0;
     float *d_synth_scale = nullptr;
+    // SPL_MODE_EXACT scratch: per query of a chunk, kExactMaxCand candidates + sort space (lazy)
+    unsigned char *d_exact = nullptr;
+    uint32_t *h_xvalid = nullptr, *m_xvalid = nullptr;  // mapped: proof flags per query of a chunk
     // batched tensor-core path scratch (lazy)
     unsigned char *d_batch = nullptr;
     BatchScratchLayout batch_layout{};
@@ -235,6 +241,7 @@ static void destroy(spl_gpu_ctx *c) {
     cudaFree(c->m.E); cudaFree(c->m.bloom); cudaFree(c->m.flags); cudaFree(c->m.epoch);
     cudaFree(c->m.E16); cudaFree(c->m.norm2);
     cudaFree(c->d_cands); cudaFree(c->d_counters); cudaFree(c->d_q); cudaFree(c->d_out); cudaFree(c->d_count);
+    cudaFree(c->d_exact); cudaFreeHost(c->h_xvalid);
     cudaFree(c->d_batch); cudaFree(c->d_qbatch); cudaFree(c->d_bout); cudaFree(c->d_bcount);
     cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount);
     cudaFree(c->d_keys); cudaFree(c->d_sort_tmp); cudaFree(c->d_big_out); cudaFree(c->d_synth_scale);
@@ -683,6 +690,68 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
     return 0;
 }
 
+// ---- SPL_MODE_EXACT ---------------------------------------------------------------------------
+struct ExactSlices {
+    spl_gpu_result *cand; uint32_t *cand_count; uint64_t *exact_key, *sort_key; uint32_t *sort_pos; uint64_t *kth;
+    uint32_t *ticket;
+};
+static constexpr size_t kExactPerQuery = kExactMaxCand * (sizeof(spl_gpu_result) + 8 + 8 + 4) + 64;
+
+static int ensure_exact_scratch(spl_gpu_ctx *c) {
+    if (c->d_exact) return 0;
+    int rc;
+    if ((rc = dev_alloc(c, &c->d_exact, kExactPerQuery * c->q_cap, true))) return rc;
+    CUDA_TRY(cudaHostAlloc((void **)&c->h_xvalid, c->q_cap * sizeof(uint32_t), cudaHostAllocMapped));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_xvalid, c->h_xvalid, 0));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+static ExactSlices exact_slices(spl_gpu_ctx *c, uint32_t qi) {
+    unsigned char *p = c->d_exact + kExactPerQuery * qi;
+    ExactSlices s;
+    s.cand = reinterpret_cast<spl_gpu_result *>(p);            p += kExactMaxCand * sizeof(spl_gpu_result);
+    s.exact_key = reinterpret_cast<uint64_t *>(p);             p += kExactMaxCand * 8;
+    s.sort_key = reinterpret_cast<uint64_t *>(p);              p += kExactMaxCand * 8;
+    s.sort_pos = reinterpret_cast<uint32_t *>(p);              p += kExactMaxCand * 4;
+    s.kth = reinterpret_cast<uint64_t *>(p);                   p += 8;
+    s.cand_count = reinterpret_cast<uint32_t *>(p);            p += 4;
+    s.ticket = reinterpret_cast<uint32_t *>(p);
+    return s;
+}
+
+// fast scan with k' candidates (thresholds relaxed by the fast-vs-sequential bound), then the exact
+// re-score + proof.  nq <= q_cap queries; caller holds c->mu.
+static int enqueue_exact(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, uint32_t nq, uint32_t kprime,
+                         spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, uint32_t *d_valid, cudaStream_t s) {
+    spl_gpu_search_params fastp = *p;
+    fastp.mode = SPL_MODE_FAST;
+    fastp.k = kprime;
+    fastp.nq = 1;
+    if (p->min_similarity > 0.f) fastp.min_similarity = p->min_similarity - kExactSimBound;
+    if (p->max_distance > 0.f) fastp.max_distance = p->max_distance * (1.f + kExactDistRel);
+    for (uint32_t qi = 0; qi < nq; qi++) {
+        const ExactSlices x = exact_slices(c, qi);
+        int rc = enqueue_fused(c, &fastp, d_q + (size_t)qi * c->dim, x.cand, kprime, x.cand_count, s);
+        if (rc) return rc;
+        ExactArgs a;
+        memset(&a, 0, sizeof a);
+        a.E = c->m.E; a.q = d_q + (size_t)qi * c->dim; a.dim = c->dim; a.order = p->order; a.k = p->k; a.kprime = kprime;
+        a.row0 = c->slot_begin; a.min_sim = p->min_similarity; a.max_dist = p->max_distance;
+        a.cand = x.cand; a.cand_count = x.cand_count; a.exact_key = x.exact_key; a.sort_key = x.sort_key;
+        a.sort_pos = x.sort_pos; a.kth_key_out = x.kth; a.ticket = x.ticket;
+        a.out = d_out + (size_t)qi * out_stride; a.out_count = d_counts + qi; a.valid = d_valid + qi;
+        CUDA_TRY(launch_exact_rescore(a, s));
+        c->launches++;
+    }
+    return 0;
+}
+
+static uint32_t exact_kprime(uint32_t k) {
+    uint32_t kp = 2 * k > k + 32 ? 2 * k : k + 32;
+    return kp > kExactMaxCand ? kExactMaxCand : kp;
+}
+
 static int ensure_batch_scratch(spl_gpu_ctx *c, uint32_t k) {
     int rc;
     if (!c->d_batch) {
@@ -744,6 +813,14 @@ extern "C" int spl_gpu_search_device(spl_gpu_ctx *c, const spl_gpu_search_params
     cudaSetDevice(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    if (p->mode == SPL_MODE_EXACT) {
+        // no host round trip is possible here, so take the widest candidate margin at once; a query whose
+        // selection still cannot be proven reports 0 hits (the host-buffer call falls back to a full exact pass)
+        if (p->k > kExactMaxK) return fail(-2, EINVAL, "device-buffer exact search needs k <= %u", kExactMaxK);
+        if (p->nq > c->q_cap) return fail(-2, EINVAL, "device-buffer exact search takes at most %u queries per call", c->q_cap);
+        if ((rc = ensure_exact_scratch(c))) return rc;
+        return enqueue_exact(c, p, d_q, p->nq, kExactMaxCand, d_out, out_stride, d_counts, c->m_xvalid, s);
+    }
     if (wants_batch(c, p)) {
         if ((rc = check_batch(c, p))) return rc;
         if (p->nq > kBatchMaxQ) return fail(-2, EINVAL, "device-buffer batched search takes at most %u queries per call", kBatchMaxQ);
@@ -769,6 +846,37 @@ static int ensure_sort_scratch(spl_gpu_ctx *c, uint32_t out_cap) {
         if ((rc = dev_alloc(c, &c->d_big_out, out_cap, false))) return rc;
         c->big_out_cap = out_cap;
     }
+    return 0;
+}
+
+// one query, every survivor scored and sorted on the device (the reference's default when --limit is absent);
+// `exact` selects the sequential-order scorer.  Caller holds c->mu.
+static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q_host, bool exact,
+                           spl_gpu_result *out, uint32_t out_stride, uint32_t *count) {
+    const uint32_t want = p->k == 0 ? out_stride : p->k;
+    const uint32_t cap = want < c->n ? want : (uint32_t)c->n;
+    int rc;
+    if ((rc = ensure_sort_scratch(c, cap))) return rc;
+    ScanArgs a;
+    fill_args(c, p, a);
+    memcpy(c->h_q, q_host, (size_t)c->dim * sizeof(float));
+    CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, (size_t)c->dim * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->d_keys, 0xFF, c->n * sizeof(uint64_t), c->stream));
+    a.q = c->d_q;
+    a.keys_out = c->d_keys;
+    a.out = c->d_big_out;
+    a.out_count = c->d_count;
+    a.k = 0;
+    if (exact) CUDA_TRY(launch_exact_all(a, c->sm_count, c->stream));
+    else CUDA_TRY(launch_scan_fast(a, c->scan_grid, c->stream));
+    CUDA_TRY(launch_sortall(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, cap, c->stream));
+    c->launches += 4;
+    CUDA_TRY(cudaMemcpyAsync(&c->h_bounce_count, c->d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    const uint32_t total = c->h_bounce_count;
+    const uint32_t ncopy = total < cap ? total : cap;
+    CUDA_TRY(cudaMemcpy(out, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost));
+    *count = p->k == 0 ? total : ncopy;
     return 0;
 }
 
@@ -822,6 +930,58 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
         }
         return 0;
     }
+    const bool exact = p->mode == SPL_MODE_EXACT;
+    if (exact && p->k >= 1 && p->k <= kExactMaxK) {
+        if ((rc = ensure_exact_scratch(c))) return rc;
+        const uint32_t kp0 = exact_kprime(p->k);
+        for (uint32_t q0 = 0; q0 < p->nq; q0 += c->q_cap) {
+            const uint32_t nq = (p->nq - q0 < c->q_cap) ? p->nq - q0 : c->q_cap;
+            memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
+            CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
+            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+            if ((rc = enqueue_exact(c, p, c->d_q, nq, kp0, c->m_out, p->k, c->m_count, c->m_xvalid, c->stream))) return rc;
+            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            if (c->timing) {
+                float ms = 0.f;
+                CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+                c->last_scan_ms = ms / nq;
+            }
+            std::vector<uint32_t> redo;
+            for (uint32_t i = 0; i < nq; i++) {
+                if (c->h_xvalid[i]) {
+                    counts[q0 + i] = c->h_count[i];
+                    memcpy(out + (size_t)(q0 + i) * out_stride, c->h_out + (size_t)i * p->k, (size_t)c->h_count[i] * sizeof(spl_gpu_result));
+                } else {
+                    redo.push_back(i);
+                }
+            }
+            // near-ties crowd the boundary: widen the candidate set once, then score every row exactly
+            for (uint32_t i : redo) {
+                bool ok = false;
+                if (kp0 < kExactMaxCand) {
+                    if ((rc = enqueue_exact(c, p, c->d_q + (size_t)i * c->dim, 1, kExactMaxCand, c->d_out, p->k, c->d_count,
+                                            c->m_xvalid, c->stream))) return rc;
+                    CUDA_TRY(cudaMemcpyAsync(c->h_bounce, c->d_out, (size_t)p->k * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost, c->stream));
+                    CUDA_TRY(cudaMemcpyAsync(&c->h_bounce_count, c->d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+                    CUDA_TRY(cudaStreamSynchronize(c->stream));
+                    if (c->h_xvalid[0]) {
+                        ok = true;
+                        counts[q0 + i] = c->h_bounce_count;
+                        memcpy(out + (size_t)(q0 + i) * out_stride, c->h_bounce, (size_t)c->h_bounce_count * sizeof(spl_gpu_result));
+                    }
+                }
+                if (!ok && (rc = search_one_full(c, p, q + (size_t)(q0 + i) * c->dim, true, out + (size_t)(q0 + i) * out_stride,
+                                                 out_stride, &counts[q0 + i]))) return rc;
+            }
+        }
+        return 0;
+    }
+    if (exact) {  // k == 0 (everything, sorted) or k > kExactMaxK: exact score of every row + device-wide sort
+        for (uint32_t qi = 0; qi < p->nq; qi++)
+            if ((rc = search_one_full(c, p, q + (size_t)qi * c->dim, true, out + (size_t)qi * out_stride, out_stride, &counts[qi]))) return rc;
+        return 0;
+    }
     if (fused) {
         // process in chunks of q_cap queries through the pinned staging buffers
         for (uint32_t q0 = 0; q0 < p->nq; q0 += c->q_cap) {
@@ -848,31 +1008,9 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
     }
     // ---- unlimited / large k: key-per-row scan + device-wide sort (cold path) ----
     uint32_t mode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
-    if (mode != SPL_MODE_FAST && mode != SPL_MODE_EXACT) return fail(-1, ENOSYS, "mode %u cannot serve k = %u", mode, p->k);
-    const uint32_t want = p->k == 0 ? out_stride : p->k;
-    const uint32_t cap = want < c->n ? want : (uint32_t)c->n;
-    if ((rc = ensure_sort_scratch(c, cap))) return rc;
-    ScanArgs a;
-    fill_args(c, p, a);
-    for (uint32_t qi = 0; qi < p->nq; qi++) {
-        memcpy(c->h_q, q + (size_t)qi * c->dim, qbytes);
-        CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, qbytes, cudaMemcpyHostToDevice, c->stream));
-        CUDA_TRY(cudaMemsetAsync(c->d_keys, 0xFF, c->n * sizeof(uint64_t), c->stream));
-        a.q = c->d_q;
-        a.keys_out = c->d_keys;
-        a.out = c->d_big_out;
-        a.out_count = c->d_count;
-        a.k = 0;
-        CUDA_TRY(launch_scan_fast(a, c->scan_grid, c->stream));
-        CUDA_TRY(launch_sortall(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, cap, c->stream));
-        c->launches += 4;
-        CUDA_TRY(cudaMemcpyAsync(c->h_count, c->d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(cudaStreamSynchronize(c->stream));
-        const uint32_t total = c->h_count[0];
-        const uint32_t ncopy = total < cap ? total : cap;
-        CUDA_TRY(cudaMemcpy(out + (size_t)qi * out_stride, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost));
-        counts[qi] = p->k == 0 ? total : ncopy;
-    }
+    if (mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "mode %u is not available for k = %u", mode, p->k);
+    for (uint32_t qi = 0; qi < p->nq; qi++)
+        if ((rc = search_one_full(c, p, q + (size_t)qi * c->dim, false, out + (size_t)qi * out_stride, out_stride, &counts[qi]))) return rc;
     return 0;
 }
 

@@ -11,7 +11,7 @@ import support
 
 pytestmark = pytest.mark.gpu
 
-MODES = [sg.MODE_FAST]
+MODES = [sg.MODE_FAST, sg.MODE_EXACT]
 
 
 @pytest.fixture(scope="module")
