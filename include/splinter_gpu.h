@@ -165,6 +165,12 @@ int spl_gpu_dense_fill_synthetic(spl_gpu_ctx *ctx, uint64_t seed_corpus, uint64_
 int spl_gpu_read_mirror(spl_gpu_ctx *ctx, uint64_t first_slot, uint64_t n, float *E,
                         uint64_t *bloom, uint8_t *flags, uint64_t *epoch);
 
+/* Resolve what the search command prints beside the scores for one hit: the slot's key, value length
+ * and type flag, as cmd_search copies them out of its snapshots (_search.c:377-383).  Store-backed
+ * contexts only; reads the live store, so a slot rewritten since the last sync shows its new key. */
+int spl_gpu_slot_meta(const spl_gpu_ctx *ctx, uint32_t slot_idx, char key_out[64], uint32_t *val_len,
+                      uint8_t *type_flag);
+
 /* ---- search ------------------------------------------------------------------------- */
 
 /* Host-buffer search (the reference-facing call).  q = nq x dim fp32.  out = nq x out_stride

@@ -367,6 +367,19 @@ extern "C" int spl_gpu_debug_timeline(spl_gpu_ctx *c, unsigned long long *out, i
     return n;
 }
 
+extern "C" int spl_gpu_slot_meta(const spl_gpu_ctx *c, uint32_t slot_idx, char key_out[64], uint32_t *val_len,
+                                 uint8_t *type_flag) {
+    if (!c || !key_out) return fail(-2, EINVAL, "null argument");
+    if (c->dense || !c->base) return fail(-2, EINVAL, "dense contexts have no keys");
+    if (slot_idx >= c->total_slots) return fail(-2, EINVAL, "slot index beyond the store");
+    const uint8_t *sl = c->base + layout::kHeaderSize + (size_t)slot_idx * c->slot_size;
+    memcpy(key_out, sl + layout::S_KEY, 64);
+    key_out[63] = '\0';
+    if (val_len) *val_len = __atomic_load_n(reinterpret_cast<const uint32_t *>(sl + layout::S_VAL_LEN), __ATOMIC_ACQUIRE);
+    if (type_flag) *type_flag = sl[24];
+    return 0;
+}
+
 extern "C" uint64_t spl_gpu_launch_count(const spl_gpu_ctx *c) { return c ? c->launches.load() : 0; }
 extern "C" int spl_gpu_set_timing(spl_gpu_ctx *c, int on) {
     if (!c) return fail(-2, EINVAL, "null context");
