@@ -48,9 +48,10 @@ typedef struct spl_gpu_ctx spl_gpu_ctx;
 #define SPL_ORDER_L2     1u /* distance asc, similarity desc, idx asc (batched L2 config) */
 
 /* ---- compute mode ------------------------------------------------------------------ */
-#define SPL_MODE_AUTO    0u /* nq < SPL_BATCH_MIN: EXACT; otherwise BATCH_BF16 when a bf16 mirror exists */
+#define SPL_MODE_AUTO    0u /* FAST; from 16 queries up BATCH_BF16 when a bf16 mirror exists and no threshold is set */
 #define SPL_MODE_FAST    1u /* fp32, per-lane partial sums + warp-shuffle tree (|d sim| ~1e-6)           */
-#define SPL_MODE_EXACT   2u /* fp32, the reference's sequential summation order: bit-identical scores   */
+#define SPL_MODE_EXACT   2u /* fp32, the reference's sequential summation order: scores and order bit-identical
+                               to the reference (fast candidate scan + sequential re-score with a selection proof) */
 #define SPL_MODE_BATCH_BF16 3u /* tcgen05 Q x E^T on the bf16 mirror, fp32 accumulate, fp32 re-rank     */
 
 /* ---- attach options ---------------------------------------------------------------- */
@@ -181,6 +182,12 @@ int spl_gpu_slot_meta(const spl_gpu_ctx *ctx, uint32_t slot_idx, char key_out[64
  * Results per query are sorted by p->order. */
 int spl_gpu_search(spl_gpu_ctx *ctx, const spl_gpu_search_params *p, const float *q,
                    spl_gpu_result *out, uint32_t out_stride, uint32_t *counts);
+
+/* How many slots survived the candidate predicate and the thresholds in each query of the most recent
+ * host-buffer spl_gpu_search on this context -- the reference's "active_keys" (result_count before the
+ * limit is applied, _search.c:408,415-424).  Exact for FAST and for k = 0; with SPL_MODE_EXACT and a
+ * threshold flag the fused path counts with the fast scores (use k = 0 when the exact count matters). */
+int spl_gpu_last_totals(const spl_gpu_ctx *ctx, uint32_t *totals, uint32_t nq);
 
 /* Device-buffer search: d_q / d_out / d_counts are device pointers on the context's device;
  * the launches are enqueued on `stream` (a cudaStream_t; NULL = the context's stream) and the

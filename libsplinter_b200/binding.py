@@ -20,7 +20,7 @@ ABI_SYMBOLS = [
     "spl_gpu_attach", "spl_gpu_attach_image", "spl_gpu_open_dense", "spl_gpu_detach", "spl_gpu_get_info",
     "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
     "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device",
-    "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta",
+    "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
 ]
 
 ORDER_COSINE, ORDER_L2 = 0, 1
@@ -104,6 +104,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_scan_noalloc.argtypes = [vp, vp, vp, vp, u64, u64, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_slot_meta.restype = C.c_int
     lib.spl_gpu_slot_meta.argtypes = [vp, u32, C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint8)]
+    lib.spl_gpu_last_totals.restype = C.c_int
+    lib.spl_gpu_last_totals.argtypes = [vp, vp, u32]
     lib.spl_gpu_launch_count.restype = u64
     lib.spl_gpu_launch_count.argtypes = [vp]
     lib.spl_gpu_set_timing.restype = C.c_int
@@ -235,6 +237,11 @@ class Mirror:
         self._check(self._lib.spl_gpu_merge_topk_device(self._h, C.c_void_p(d_lists), C.c_void_p(d_counts), nlists,
                                                         stride, order, k, C.c_void_p(d_out), C.c_void_p(d_out_count),
                                                         C.c_void_p(stream)))
+
+    def last_totals(self, nq=1):
+        t = np.zeros(nq, np.uint32)
+        self._check(self._lib.spl_gpu_last_totals(self._h, _ptr(t), nq))
+        return t
 
     def launch_count(self) -> int:
         return int(self._lib.spl_gpu_launch_count(self._h))

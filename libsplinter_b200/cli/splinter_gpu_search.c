@@ -199,7 +199,10 @@ int main(int argc, char **argv) {
     memset(&p, 0, sizeof p);
     p.struct_size = sizeof p; p.nq = 1; p.dim = info.dim;
     /* the regex is applied before the limit in the reference (:365-368 then :415-416): ask for everything then */
-    p.k = (limit > 0 && !have_rx && embedding_available) ? (uint32_t)limit : 0;
+    /* ... and "active_keys" counts every survivor; the fused top-k path reports that count exactly unless a
+     * threshold flag is active (then the sorted full pass is used). */
+    const int thresholds = min_similarity > 0.0f || max_distance > 0.0f;
+    p.k = (limit > 0 && !have_rx && embedding_available && !thresholds) ? (uint32_t)limit : 0;
     p.order = SPL_ORDER_COSINE; p.mode = SPL_MODE_EXACT; p.bloom_mask = bloom_mask;
     p.min_similarity = embedding_available ? min_similarity : 0.f;
     p.max_distance = embedding_available ? max_distance : 0.f;
@@ -208,6 +211,8 @@ int main(int argc, char **argv) {
     hits = calloc(cap, sizeof *hits);
     if (spl_gpu_search(gpu, &p, query_vec, hits, cap, &n_hits) != 0) { fprintf(stderr, "search: %s\n", spl_gpu_last_error()); goto cleanup; }
     if (n_hits > cap) n_hits = cap;
+    uint32_t total_survivors = n_hits;
+    if (p.k) spl_gpu_last_totals(gpu, &total_survivors, 1);
 
     /* resolve keys, apply the regex, then the limit */
     meta = calloc(n_hits ? n_hits : 1, sizeof *meta);
@@ -223,7 +228,8 @@ int main(int argc, char **argv) {
         hits[result_count] = hits[i];
         meta[result_count++] = m;
     }
-    uint32_t print_count = result_count;
+    if (p.k) result_count = total_survivors;   /* nothing was filtered on the host in this case */
+    uint32_t print_count = p.k ? n_hits : result_count;
     if (limit > 0 && print_count > (uint32_t)limit) print_count = (uint32_t)limit;
 
     /* ---- output: format strings of _search.c:419-473 ---- */

@@ -49,16 +49,21 @@ __global__ void __launch_bounds__(32) exact_rescore_kernel(const ExactArgs a) {
             reinterpret_cast<float4 *>(sq)[i] = q4[i];
         }
         __syncwarp();
+        // lanes 0..3: dot, mag_a, mag_b, sum -- same instruction stream, operands picked by lane (no divergence)
         float acc = 0.0f;
-        if (lane < 4) {
-            for (uint32_t d = 0; d < a.dim; d++) {
-                const float x = sq[d], y = srow[d];   // a = query, b = slot vector (_search.c:395-396)
-                float term;
-                if (lane == 0) term = __fmul_rn(x, y);
-                else if (lane == 1) term = __fmul_rn(x, x);
-                else if (lane == 2) term = __fmul_rn(y, y);
-                else { const float diff = __fsub_rn(x, y); term = __fmul_rn(diff, diff); }
-                acc = __fadd_rn(acc, term);
+        const float4 *sq4 = reinterpret_cast<const float4 *>(sq), *sr4 = reinterpret_cast<const float4 *>(srow);
+        const bool l1 = lane == 1, l2 = lane == 2, l3 = lane == 3;
+#pragma unroll 4
+        for (uint32_t i = 0; i < a.dim / 4; i++) {
+            const float4 xq = sq4[i], yr = sr4[i];   // a = query, b = slot vector (_search.c:395-396)
+            const float xs[4] = { xq.x, xq.y, xq.z, xq.w }, ys[4] = { yr.x, yr.y, yr.z, yr.w };
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float x = xs[j], y = ys[j];
+                const float diff = __fsub_rn(x, y);
+                const float u = l3 ? diff : (l2 ? y : x);
+                const float v = l3 ? diff : (l1 ? x : y);
+                acc = __fadd_rn(acc, __fmul_rn(u, v));   // strictly in index order, no FMA
             }
         }
         const float dot = __shfl_sync(0xffffffffu, acc, 0), ma = __shfl_sync(0xffffffffu, acc, 1);
@@ -78,6 +83,9 @@ __global__ void __launch_bounds__(32) exact_rescore_kernel(const ExactArgs a) {
     if (!s_last) return;
     __threadfence();
     if (lane == 0) *a.ticket = 0;
+    // stage the candidates' slot indices and has_embedding flags in shared memory for the sort below
+    __shared__ uint64_t s_key[kExactMaxCand];
+    __shared__ uint32_t s_slot[kExactMaxCand], s_pos[kExactMaxCand];
     // thresholds apply to the exact scores (a candidate can sit on either side of one by an ulp)
     uint32_t kept = 0;
     for (uint32_t base = 0; base < ncand; base += 32) {
@@ -99,8 +107,9 @@ __global__ void __launch_bounds__(32) exact_rescore_kernel(const ExactArgs a) {
         const unsigned m = __ballot_sync(0xffffffffu, keep);
         if (keep) {
             const uint32_t pos = kept + __popc(m & ((1u << lane) - 1u));
-            a.sort_key[pos] = key;
-            a.sort_pos[pos] = i;
+            s_key[pos] = key;
+            s_pos[pos] = i;
+            s_slot[pos] = a.cand[i].slot_idx;
         }
         kept += __popc(m);
     }
@@ -111,10 +120,10 @@ __global__ void __launch_bounds__(32) exact_rescore_kernel(const ExactArgs a) {
     for (uint32_t base = 0; base < kept; base += 32) {
         const uint32_t i = base + lane;
         if (i < kept) {
-            const uint64_t key = a.sort_key[i];
-            const uint32_t pos = a.sort_pos[i], slot = a.cand[pos].slot_idx;
+            const uint64_t key = s_key[i];
+            const uint32_t pos = s_pos[i], slot = s_slot[i];
             uint32_t rank = 0;
-            for (uint32_t j = 0; j < kept; j++) rank += better(a.sort_key[j], a.cand[a.sort_pos[j]].slot_idx, key, slot) ? 1u : 0u;
+            for (uint32_t j = 0; j < kept; j++) rank += better(s_key[j], s_slot[j], key, slot) ? 1u : 0u;
             if (rank < nout) {
                 spl_gpu_result r = a.cand[pos];
                 split_key(a.order, key, r.similarity, r.distance);

@@ -106,6 +106,8 @@ struct spl_gpu_ctx {
     uint32_t *d_count = nullptr, *h_count = nullptr;
     spl_gpu_result h_bounce[SPL_GPU_KMAX_FUSED];  // small host bounce buffers for the retry paths
     uint32_t h_bounce_count = 0;
+    uint32_t *h_total = nullptr, *m_total = nullptr;  // mapped: rows that survived predicate + thresholds, per query
+    uint32_t last_nq = 0;
     spl_gpu_result *m_out = nullptr;  // device views of the mapped host buffers h_out / h_count
     uint32_t *m_count = nullptr;
     uint32_t q_cap = 0, out_cap = 0;
@@ -208,6 +210,9 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     CUDA_TRY(cudaHostAlloc((void **)&c->h_count, (size_t)c->q_cap * sizeof(uint32_t), cudaHostAllocMapped));
     CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_out, c->h_out, 0));
     CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_count, c->h_count, 0));
+    CUDA_TRY(cudaHostAlloc((void **)&c->h_total, (size_t)kMaxBatchQ * sizeof(uint32_t), cudaHostAllocMapped));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_total, c->h_total, 0));
+    memset(c->h_total, 0, (size_t)kMaxBatchQ * sizeof(uint32_t));
     // staging for sync / dense upload
     if (c->sync_threads == 0) {
         unsigned hc = std::thread::hardware_concurrency();
@@ -245,7 +250,7 @@ static void destroy(spl_gpu_ctx *c) {
     cudaFree(c->d_batch); cudaFree(c->d_qbatch); cudaFree(c->d_bout); cudaFree(c->d_bcount);
     cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount);
     cudaFree(c->d_keys); cudaFree(c->d_sort_tmp); cudaFree(c->d_big_out); cudaFree(c->d_synth_scale);
-    cudaFreeHost(c->h_q); cudaFreeHost(c->h_out); cudaFreeHost(c->h_count);
+    cudaFreeHost(c->h_q); cudaFreeHost(c->h_out); cudaFreeHost(c->h_count); cudaFreeHost(c->h_total);
     for (StageBuf &b : c->stage) {
         cudaFreeHost(b.h_rows); cudaFreeHost(b.h_meta); cudaFree(b.d_rows); cudaFree(b.d_meta);
         if (b.ev) cudaEventDestroy(b.ev);
@@ -377,6 +382,13 @@ extern "C" int spl_gpu_slot_meta(const spl_gpu_ctx *c, uint32_t slot_idx, char k
     key_out[63] = '\0';
     if (val_len) *val_len = __atomic_load_n(reinterpret_cast<const uint32_t *>(sl + layout::S_VAL_LEN), __ATOMIC_ACQUIRE);
     if (type_flag) *type_flag = sl[24];
+    return 0;
+}
+
+extern "C" int spl_gpu_last_totals(const spl_gpu_ctx *c, uint32_t *totals, uint32_t nq) {
+    if (!c || !totals) return fail(-2, EINVAL, "null argument");
+    if (nq > kMaxBatchQ) nq = kMaxBatchQ;
+    memcpy(totals, c->h_total, (size_t)nq * sizeof(uint32_t));
     return 0;
 }
 
@@ -686,7 +698,7 @@ static void fill_args(const spl_gpu_ctx *c, const spl_gpu_search_params *p, Scan
 
 // enqueue one fused top-k scan per query (k in 1..KMAX_FUSED); caller holds c->mu
 static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, spl_gpu_result *d_out,
-                         uint32_t out_stride, uint32_t *d_counts, cudaStream_t s) {
+                         uint32_t out_stride, uint32_t *d_counts, cudaStream_t s, uint32_t *d_totals = nullptr) {
     uint32_t mode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
     if (mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "mode %u is not available for this query shape", mode);
     ScanArgs a;
@@ -696,6 +708,7 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         a.q = d_q + (size_t)qi * c->dim;
         a.out = d_out + (size_t)qi * out_stride;
         a.out_count = d_counts + qi;
+        a.total = d_totals ? d_totals + qi : nullptr;
         if (!c->force_ldg && scan_tma_supported(a.dim, a.k)) CUDA_TRY(launch_scan_tma(a, c->sm_count, s));
         else CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
         c->launches++;
@@ -736,7 +749,8 @@ static ExactSlices exact_slices(spl_gpu_ctx *c, uint32_t qi) {
 // fast scan with k' candidates (thresholds relaxed by the fast-vs-sequential bound), then the exact
 // re-score + proof.  nq <= q_cap queries; caller holds c->mu.
 static int enqueue_exact(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, uint32_t nq, uint32_t kprime,
-                         spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, uint32_t *d_valid, cudaStream_t s) {
+                         spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, uint32_t *d_valid, cudaStream_t s,
+                         uint32_t *d_totals = nullptr) {
     spl_gpu_search_params fastp = *p;
     fastp.mode = SPL_MODE_FAST;
     fastp.k = kprime;
@@ -745,7 +759,8 @@ static int enqueue_exact(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
     if (p->max_distance > 0.f) fastp.max_distance = p->max_distance * (1.f + kExactDistRel);
     for (uint32_t qi = 0; qi < nq; qi++) {
         const ExactSlices x = exact_slices(c, qi);
-        int rc = enqueue_fused(c, &fastp, d_q + (size_t)qi * c->dim, x.cand, kprime, x.cand_count, s);
+        int rc = enqueue_fused(c, &fastp, d_q + (size_t)qi * c->dim, x.cand, kprime, x.cand_count, s,
+                               d_totals ? d_totals + qi : nullptr);
         if (rc) return rc;
         ExactArgs a;
         memset(&a, 0, sizeof a);
@@ -761,6 +776,7 @@ static int enqueue_exact(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
 }
 
 static uint32_t exact_kprime(uint32_t k) {
+    if (k <= 16) return 32;  // stays on the scan's register/shuffle epilogue (k' <= 32)
     uint32_t kp = 2 * k > k + 32 ? 2 * k : k + 32;
     return kp > kExactMaxCand ? kExactMaxCand : kp;
 }
@@ -890,6 +906,7 @@ static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const
     const uint32_t ncopy = total < cap ? total : cap;
     CUDA_TRY(cudaMemcpy(out, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost));
     *count = p->k == 0 ? total : ncopy;
+    c->h_total[0] = total;  // the sorted pass counts every survivor
     return 0;
 }
 
@@ -952,7 +969,8 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
             CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
-            if ((rc = enqueue_exact(c, p, c->d_q, nq, kp0, c->m_out, p->k, c->m_count, c->m_xvalid, c->stream))) return rc;
+            memset(c->h_total + q0, 0, nq * sizeof(uint32_t));
+            if ((rc = enqueue_exact(c, p, c->d_q, nq, kp0, c->m_out, p->k, c->m_count, c->m_xvalid, c->stream, c->m_total + q0))) return rc;
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
             CUDA_TRY(cudaStreamSynchronize(c->stream));
             if (c->timing) {
@@ -1004,7 +1022,8 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
             CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
-            if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream))) return rc;
+            memset(c->h_total + q0, 0, nq * sizeof(uint32_t));  // mapped memory; ordered before the launch below
+            if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream, c->m_total + q0))) return rc;
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
             CUDA_TRY(cudaStreamSynchronize(c->stream));
             if (c->timing) {

@@ -66,6 +66,7 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_kernel(const ScanAr
         f = 0; b = 0;
         if (g < ngroups && row < a.n) { f = a.flags[row]; b = a.bloom[row]; }
     };
+    uint32_t nsurv = 0;
     auto finish_row = [&](uint32_t row, uint32_t f, float dot, float mb, float ss) {
         float sim, dist;
         if (f & SPL_ROW_EMB) {
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_kernel(const ScanAr
             if (thresholds) return;
             sim = 0.f; dist = FLT_MAX;
         }
+        nsurv++;
         const uint64_t key = make_key(a.order, sim, dist);
         if (KEYS) {  // unlimited / large-k path: publish the key, a device-wide sort follows
             if (lane == 0) a.keys_out[row] = key;
@@ -146,12 +148,13 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_kernel(const ScanAr
         }
         g = gn; f = fn; b = bn;
     }
+    if (a.total && lane == 0 && nsurv) atomicAdd(&a.counters[2], nsurv);
     if (KEYS) {
         // re-arm the work counter once every CTA has drained it
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
-            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) { a.counters[0] = 0; a.counters[1] = 0; }
+            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) { a.counters[0] = 0; a.counters[1] = 0; a.counters[2] = 0; }
         }
         return;
     }
@@ -184,6 +187,7 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_generic_kernel(cons
     const uint32_t ngroups = (a.n + 31u) >> 5;
     const float4 *E4 = reinterpret_cast<const float4 *>(a.E);
     const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+    uint32_t nsurv = 0;
     for (;;) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&a.counters[0], 1u);
@@ -220,6 +224,7 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_generic_kernel(cons
                 keep = !thresholds; sim = 0.f; dist = FLT_MAX;
             }
             if (keep) {
+                nsurv++;
                 const uint64_t key = make_key(a.order, sim, dist);
                 if (KEYS) {
                     if (lane == 0) a.keys_out[r0] = key;
@@ -229,11 +234,12 @@ __global__ void __launch_bounds__(kScanThreads, 3) scan_fast_generic_kernel(cons
             }
         }
     }
+    if (a.total && lane == 0 && nsurv) atomicAdd(&a.counters[2], nsurv);
     if (KEYS) {
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
-            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) { a.counters[0] = 0; a.counters[1] = 0; }
+            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) { a.counters[0] = 0; a.counters[1] = 0; a.counters[2] = 0; }
         }
         return;
     }

@@ -26,6 +26,8 @@ struct ScanArgs {
     // unlimited / large-k path: when non-null the kernel writes one key per surviving row here
     // (pre-filled with kKeySentinel by the caller) instead of keeping a top-k
     uint64_t *keys_out;
+    uint32_t *total;         // nullable: where the LAST CTA stores the number of rows that passed predicate and
+                             // thresholds (accumulated in counters[2]; may point to mapped host memory)
     uint32_t chunk_groups;   // TMA kernel: 32-slot groups handed out per work-counter increment (1..8)
     // developer timeline (nullable): per CTA {start, producers done, consumers done, end} in ns
     unsigned long long *dbg;

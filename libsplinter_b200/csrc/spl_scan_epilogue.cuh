@@ -133,7 +133,10 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
     }
     cta_tree_merge32<NW>(key, idx, xk, xi);
     if (warp == 0) {
-        if (lane == 0) { a.counters[0] = 0; a.counters[1] = 0; }
+        if (lane == 0) {
+            if (a.total) *a.total = *reinterpret_cast<volatile uint32_t *>(&a.counters[2]);
+            a.counters[0] = 0; a.counters[1] = 0; a.counters[2] = 0;
+        }
         const unsigned valid = __ballot_sync(0xffffffffu, lane < k && idx != kIdxSentinel);
         if (lane == 0) *a.out_count = __popc(valid);
         if (lane < k && idx != kIdxSentinel) {
@@ -194,7 +197,10 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
         __syncthreads();
         bitonic_sort_cta(ws_keys, ws_idx, W);  // running top-k stays in [0, k)
     }
-    if (threadIdx.x == 0) { a.counters[0] = 0; a.counters[1] = 0; }
+    if (threadIdx.x == 0) {
+        if (a.total) *a.total = *reinterpret_cast<volatile uint32_t *>(&a.counters[2]);
+        a.counters[0] = 0; a.counters[1] = 0; a.counters[2] = 0;
+    }
     uint32_t cnt = 0;
     for (uint32_t t = threadIdx.x; t < k; t += blockDim.x) {
         const uint32_t idx = ws_idx[t];

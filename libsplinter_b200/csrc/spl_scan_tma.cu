@@ -248,6 +248,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         }
         ma = warp_sum(ma);
         const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+        uint32_t nsurv = 0;  // rows that passed predicate + thresholds (the reference's "active_keys")
         auto finish = [&](uint32_t row, uint32_t f, float dot, float mb, float ss) {
             float sim, dist;
             if (f & SPL_ROW_EMB) {
@@ -259,6 +260,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                 if (thresholds) return;
                 sim = 0.f; dist = FLT_MAX;
             }
+            nsurv++;
             const uint64_t key = make_key(a.order, sim, dist);
             if (W.admits(key, row)) W.insert(key, row, lane);
         };
@@ -309,6 +311,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
             finish(mt.x, mt.y, d0, e0, s0);
             if (two) finish(mt.z, mt.w, d1, e1, s1);
         }
+        if (a.total && lane == 0 && nsurv) atomicAdd(&a.counters[2], nsurv);
     }
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 4 + 2] = gtime();
     // the row ring is idle now: it becomes the workspace of the final cross-CTA merge
