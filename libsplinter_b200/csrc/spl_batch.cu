@@ -28,6 +28,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <float.h>
+#include <stdlib.h>
 
 #include "spl_batch.cuh"
 #include "spl_scan_epilogue.cuh"
@@ -67,6 +68,33 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address: "CTA 0 of the pair"
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+    // issued by both CTAs of a pair; the bytes are accounted on the LEADER's mbarrier
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bar_arrive_leader(uint32_t b) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(b & kPeerBitMask) : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {  // arrives on the same barrier in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -100,47 +128,78 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 // kind::f16 instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate (bit 4), A = B = bf16
 // (bits 7, 10), both K-major, N >> 3 at [17,23), M >> 4 at [24,29).
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+constexpr uint32_t kIdescPair = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+// pair variant: each CTA stages its own 128 queries (16 KB) and HALF of the 256-row operand (16 KB)
+constexpr int kStagesPair = 6;
+constexpr uint32_t kStageBPair = (BN / 2) * BK * 2, kStageBytesPair = kStageA + kStageBPair;
+struct GemmSmemPair {
+    static constexpr uint32_t coef_off = kStagesPair * kStageBytesPair;
+    static constexpr uint32_t bar_off = coef_off + 2 * 2 * BN * 4;
+    static constexpr uint32_t total = bar_off + 256;
+};
 
 }  // namespace
 
 // -------------------------------------------------------------------------------------------------
+// PAIR = false: one CTA = 128 queries x 256 rows per tile (cta_group::1).
+// PAIR = true : a 2-CTA cluster = 256 queries x 256 rows per tile (cta_group::2, M = 256): each CTA stages its own
+//               128 queries and half of the row operand, so the bytes every SM pulls from L2 per MMA drop by a third
+//               and six stages fit; CTA 0 issues the MMAs for both, each CTA drains its own 128 TMEM lanes.
+template <bool PAIR>
 __global__ void __launch_bounds__(kThreadsGemm, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapE, const BatchArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ uint32_t s_tmem_base;
+    constexpr uint32_t NS = PAIR ? kStagesPair : kStages;
+    constexpr uint32_t STAGE = PAIR ? kStageBytesPair : kStageBytes;
+    constexpr uint32_t COEF_OFF = PAIR ? GemmSmemPair::coef_off : GemmSmem::coef_off;
+    constexpr uint32_t BAR_OFF = PAIR ? GemmSmemPair::bar_off : GemmSmem::bar_off;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t bars = s32(smem + GemmSmem::bar_off);
-    // barrier map: full[s] 0..3, empty[s] 4..7, tfull[a] 8..9, tempty[a] 10..11, cfull[c] 12..13, cempty[c] 14..15
+    const uint32_t crank = PAIR ? cluster_rank() : 0u;
+    const bool leader = crank == 0;
+    const uint32_t bars = s32(smem + BAR_OFF);
+    // barrier map: full[s] 0..5, empty[s] 6..11, tfull[a] 12..13, tempty[a] 14..15, cfull[c] 16..17, cempty[c] 18..19
     auto FULL = [&](uint32_t s) { return bars + 8 * s; };
-    auto EMPTY = [&](uint32_t s) { return bars + 8 * (4 + s); };
-    auto TFULL = [&](uint32_t x) { return bars + 8 * (8 + x); };
-    auto TEMPTY = [&](uint32_t x) { return bars + 8 * (10 + x); };
-    auto CFULL = [&](uint32_t x) { return bars + 8 * (12 + x); };
-    auto CEMPTY = [&](uint32_t x) { return bars + 8 * (14 + x); };
-    float *cA = reinterpret_cast<float *>(smem + GemmSmem::coef_off);  // [2][BN]
-    float *cB = cA + 2 * BN;                                          // [2][BN]
+    auto EMPTY = [&](uint32_t s) { return bars + 8 * (6 + s); };
+    auto TFULL = [&](uint32_t x) { return bars + 8 * (12 + x); };
+    auto TEMPTY = [&](uint32_t x) { return bars + 8 * (14 + x); };
+    auto CFULL = [&](uint32_t x) { return bars + 8 * (16 + x); };
+    auto CEMPTY = [&](uint32_t x) { return bars + 8 * (18 + x); };
+    float *cA = reinterpret_cast<float *>(smem + COEF_OFF);  // [2][BN]
+    float *cB = cA + 2 * BN;                                 // [2][BN]
 
     if (threadIdx.x == 0) {
-        for (uint32_t s = 0; s < kStages; s++) { bar_init(FULL(s), 1); bar_init(EMPTY(s), 1); }
+        // PAIR: the leader's FULL barrier collects its own arrive.expect_tx + the peer's remote arrive, and its
+        // TEMPTY barrier the 4 epilogue warps of BOTH CTAs
+        for (uint32_t s = 0; s < NS; s++) { bar_init(FULL(s), PAIR ? 2 : 1); bar_init(EMPTY(s), 1); }
         for (uint32_t x = 0; x < kAcc; x++) {
-            bar_init(TFULL(x), 1); bar_init(TEMPTY(x), 4);
+            bar_init(TFULL(x), 1); bar_init(TEMPTY(x), PAIR ? 8 : 4);
             bar_init(CFULL(x), 64); bar_init(CEMPTY(x), 4);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {  // TMEM allocation: one warp, result lands in shared memory
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&s_tmem_base)), "n"(kTmemCols));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (warp == 2) {  // TMEM allocation: one warp (the same warp index in both CTAs of a pair)
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&s_tmem_base)), "n"(kTmemCols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&s_tmem_base)), "n"(kTmemCols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();  // the peer's barriers must be initialised before anything signals them
     tc_fence_after();
     const uint32_t tmem_base = s_tmem_base;
 
-    // ---- static tile schedule: CTA = (query tile, group); groups stride over the tile list ----
-    const uint32_t qtile = blockIdx.x % a.n_qtiles, group = blockIdx.x / a.n_qtiles, ngroups = gridDim.x / a.n_qtiles;
+    // ---- static tile schedule: unit = CTA (or CTA pair) = (query tile [pair], group); groups stride over the tiles ----
+    const uint32_t unit = PAIR ? blockIdx.x / 2 : blockIdx.x, nunits = PAIR ? gridDim.x / 2 : gridDim.x;
+    const uint32_t qunits = PAIR ? a.n_qtiles / 2 : a.n_qtiles;   // query tiles (pairs of tiles) in flight
+    const uint32_t qtile = PAIR ? (unit % qunits) * 2 + crank : unit % qunits;
+    const uint32_t group = unit / qunits, ngroups = nunits / qunits;
     const uint32_t kblocks = a.dim / BK;
-    const bool active = group < ngroups;  // CTAs beyond a whole number of groups idle
+    const bool active = group < ngroups;  // units beyond a whole number of groups idle
 
     if (warp == 0) {
         if (lane == 0 && active) {
@@ -149,17 +208,25 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 const int row0 = (int)((a.tile_first + j * a.tile_stride) * BN);
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
                     bar_wait(EMPTY(st), ph ^ 1u);
-                    bar_expect_tx(FULL(st), kStageBytes);
-                    const uint32_t sa = s32(smem + st * kStageBytes), sb = sa + kStageA;
+                    const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
                     // both operands are stored tiled ([tile][k-block][rows][64]): each stage is one contiguous burst
-                    tma_load_2d(sa, &mapQ, FULL(st), 0, (int)((qtile * kblocks + kb) * BM));
-                    tma_load_2d(sb, &mapE, FULL(st), 0, (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN));
-                    if (++st == kStages) { st = 0; ph ^= 1u; }
+                    if (PAIR) {
+                        if (leader) bar_expect_tx(FULL(st), 2 * STAGE);   // both CTAs' bytes land on the leader's barrier
+                        else bar_arrive_leader(FULL(st));
+                        tma_load_2d_pair(sa, &mapQ, FULL(st), 0, (int)((qtile * kblocks + kb) * BM));
+                        tma_load_2d_pair(sb, &mapE, FULL(st), 0,
+                                         (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN + crank * (BN / 2)));
+                    } else {
+                        bar_expect_tx(FULL(st), STAGE);
+                        tma_load_2d(sa, &mapQ, FULL(st), 0, (int)((qtile * kblocks + kb) * BM));
+                        tma_load_2d(sb, &mapE, FULL(st), 0, (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN));
+                    }
+                    if (++st == NS) { st = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && active) {
+        if (lane == 0 && active && leader) {
             uint32_t st = 0, ph = 0, acc = 0, aph = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 bar_wait(TEMPTY(acc), aph ^ 1u);
@@ -167,15 +234,18 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
                     bar_wait(FULL(st), ph);
                     tc_fence_after();
-                    const uint32_t sa = s32(smem + st * kStageBytes), sb = sa + kStageA;
+                    const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
                     const uint64_t da = make_desc(sa), db = make_desc(sb);
 #pragma unroll
-                    for (uint32_t k = 0; k < BK / UK; k++)
-                        tc_mma_f16(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
-                    tc_commit(EMPTY(st));  // the stage is free once these MMAs have read it
-                    if (++st == kStages) { st = 0; ph ^= 1u; }
+                    for (uint32_t k = 0; k < BK / UK; k++) {
+                        if (PAIR) tc_mma_f16_pair(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdescPair, (kb | k) != 0 ? 1u : 0u);
+                        else tc_mma_f16(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    // the stage is free (in both CTAs of a pair) once these MMAs have read it
+                    if (PAIR) tc_commit_pair(EMPTY(st)); else tc_commit(EMPTY(st));
+                    if (++st == NS) { st = 0; ph ^= 1u; }
                 }
-                tc_commit(TFULL(acc));     // accumulator complete
+                if (PAIR) tc_commit_pair(TFULL(acc)); else tc_commit(TFULL(acc));  // accumulator complete
                 if (++acc == kAcc) { acc = 0; aph ^= 1u; }
             }
         }
@@ -252,7 +322,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) { bar_arrive(TEMPTY(acc)); bar_arrive(CEMPTY(acc)); }
+                if (lane == 0) {
+                    if (PAIR) bar_arrive_leader(TEMPTY(acc)); else bar_arrive(TEMPTY(acc));  // the leader's MMA waits for both CTAs
+                    bar_arrive(CEMPTY(acc));
+                }
                 if (a.pass == 1 && qvalid) {
                     a.tile_min[(size_t)j * a.nq_pad + q] = tmin;
                     a.tile_min_row[(size_t)j * a.nq_pad + q] = imin;
@@ -263,9 +336,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();  // neither CTA may free TMEM / exit while the other still uses the pair
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
     }
 }
 
@@ -402,7 +477,28 @@ static bool make_map(CUtensorMap *map, const void *base, uint64_t rows, uint32_t
 }
 
 cudaError_t batch_prepare() {
-    return cudaFuncSetAttribute(gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmem::total);
+    cudaError_t e = cudaFuncSetAttribute(gemm_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmem::total);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmemPair::total);
+}
+
+static cudaError_t launch_gemm(const CUtensorMap &mapQ, const CUtensorMap &mapE, const BatchArgs &a, bool pair, int grid,
+                               cudaStream_t s) {
+    if (!pair) {
+        gemm_topk_kernel<false><<<grid, kThreadsGemm, GemmSmem::total, s>>>(mapQ, mapE, a);
+        return cudaGetLastError();
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreadsGemm);
+    cfg.dynamicSmemBytes = GemmSmemPair::total;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, gemm_topk_kernel<true>, mapQ, mapE, a);
 }
 
 bool batch_supported(uint32_t dim, uint32_t k) { return dim % BK == 0 && dim >= BK && k >= 1 && k <= 128; }
@@ -446,7 +542,10 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
 
     CUtensorMap mapQ, mapE;
     const uint64_t n_pad = ((uint64_t)a.n + BN - 1) / BN * BN;
-    if (!make_map(&mapQ, q16, a.nq_pad, a.dim, BM) || !make_map(&mapE, a.E16, n_pad, a.dim, BN)) return cudaErrorNotSupported;
+    // 256 queries and up run on CTA pairs (cta_group::2); the row operand is then fetched in two 128-row halves
+    const bool pair = a.n_qtiles % 2 == 0 && getenv("SPL_GPU_BATCH_1CTA") == nullptr;
+    if (!make_map(&mapQ, q16, a.nq_pad, a.dim, BM) || !make_map(&mapE, a.E16, n_pad, a.dim, pair ? BN / 2 : BN))
+        return cudaErrorNotSupported;
 
     cudaError_t e;
     qprep_kernel<<<a.nq_pad, 256, 0, s>>>(d_q32, a.nq, a.nq_pad, a.dim, q16);
@@ -457,6 +556,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     const uint32_t tiles = (a.n + BN - 1) / BN;
     int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;
     if (grid < (int)a.n_qtiles) grid = (int)a.n_qtiles;
+    if (pair) grid &= ~1;
     // pass 1: a PREFIX of the tiles (all of them when the shard is small) -> per-tile minima -> thresholds.
     // With a 1/f sample the expected survivors of pass 2 are ~ f * k'; a prefix (not a strided sample) keeps
     // that true for ties on t as well, because the bound is the pair (t, row).
@@ -466,16 +566,14 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     if (sampled < 4 * kprime) sampled = 4 * kprime;
     if (sampled > tiles) sampled = tiles;
     a.pass = 1; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = sampled;
-    gemm_topk_kernel<<<grid, kThreadsGemm, GemmSmem::total, s>>>(mapQ, mapE, a);
-    if ((e = cudaGetLastError())) return e;
+    if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
     threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, kprime, a.thr,
                                                        a.thr_row);
     if ((e = cudaGetLastError())) return e;
     // pass 2: every tile, append what beats the threshold
     a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
-    gemm_topk_kernel<<<grid, kThreadsGemm, GemmSmem::total, s>>>(mapQ, mapE, a);
-    if ((e = cudaGetLastError())) return e;
+    if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     static bool attr = false;
     const size_t sel_smem = (size_t)kBatchCandCap * 12;
     if (!attr) {
