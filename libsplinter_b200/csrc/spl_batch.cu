@@ -303,19 +303,37 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 float tmin = INFINITY;
                 uint32_t imin = kIdxSentinel;
 #pragma unroll 1
-                for (uint32_t c0 = 0; c0 < BN; c0 += 32) {
+                for (uint32_t c0 = 0; c0 < (a.pass == 3 ? 0u : (uint32_t)BN); c0 += 32) {  // pass 3: developer probe, no epilogue math
                     uint32_t v[32];
                     tc_ld32(tmem_base + ((quad * 32u) << 16) + acc * BN + c0, v);
+                    const float4 *pa4 = reinterpret_cast<const float4 *>(pa + c0), *pb4 = reinterpret_cast<const float4 *>(pb + c0);
+                    // branch-free common path: ordering values + their minimum over the 32 columns
+                    float cmin = INFINITY;
 #pragma unroll
-                    for (int i = 0; i < 32; i++) {
-                        const float t = fmaf(__uint_as_float(v[i]), pa[c0 + i], pb[c0 + i]);
-                        if (a.pass == 1) {
-                            if (t < tmin) { tmin = t; imin = row0 + c0 + i; }  // first (lowest) row of the minimum
-                        } else if (t <= thr && (t < thr || row0 + c0 + i <= thr_row)) {
-                            const uint32_t pos = atomicAdd(&a.cand_cnt[q], 1u);
-                            if (pos < a.cand_cap) {
-                                a.cand_t[(size_t)q * a.cand_cap + pos] = t;
-                                a.cand_idx[(size_t)q * a.cand_cap + pos] = row0 + c0 + i;
+                    for (int i4 = 0; i4 < 8; i4++) {
+                        const float4 ca = pa4[i4], cb = pb4[i4];
+                        float t0 = fmaf(__uint_as_float(v[4 * i4 + 0]), ca.x, cb.x), t1 = fmaf(__uint_as_float(v[4 * i4 + 1]), ca.y, cb.y);
+                        float t2 = fmaf(__uint_as_float(v[4 * i4 + 2]), ca.z, cb.z), t3 = fmaf(__uint_as_float(v[4 * i4 + 3]), ca.w, cb.w);
+                        v[4 * i4 + 0] = __float_as_uint(t0); v[4 * i4 + 1] = __float_as_uint(t1);
+                        v[4 * i4 + 2] = __float_as_uint(t2); v[4 * i4 + 3] = __float_as_uint(t3);
+                        cmin = fminf(cmin, fminf(fminf(t0, t1), fminf(t2, t3)));
+                    }
+                    if (a.pass == 1) {
+                        if (cmin < tmin) {   // rare after the first few tiles: find the first column holding the new minimum
+                            tmin = cmin;
+#pragma unroll
+                            for (int i = 31; i >= 0; i--) if (__uint_as_float(v[i]) == cmin) imin = row0 + c0 + i;
+                        }
+                    } else if (cmin <= thr) {  // some column of this chunk may beat the bound (static register indexing)
+#pragma unroll
+                        for (int i = 0; i < 32; i++) {
+                            const float t = __uint_as_float(v[i]);
+                            if (t <= thr && (t < thr || row0 + c0 + i <= thr_row)) {
+                                const uint32_t pos = atomicAdd(&a.cand_cnt[q], 1u);
+                                if (pos < a.cand_cap) {
+                                    a.cand_t[(size_t)q * a.cand_cap + pos] = t;
+                                    a.cand_idx[(size_t)q * a.cand_cap + pos] = row0 + c0 + i;
+                                }
                             }
                         }
                     }
@@ -572,7 +590,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
                                                        a.thr_row);
     if ((e = cudaGetLastError())) return e;
     // pass 2: every tile, append what beats the threshold
-    a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
+    a.pass = getenv("SPL_GPU_BATCH_PROBE") ? 3 : 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     static bool attr = false;
     const size_t sel_smem = (size_t)kBatchCandCap * 12;
