@@ -150,6 +150,18 @@ const char *spl_gpu_last_error(void);
  * splinter.c:843).  May run concurrently with spl_gpu_search from other threads. */
 int spl_gpu_sync(spl_gpu_ctx *ctx, spl_gpu_sync_stats *stats /* nullable */);
 
+/* Sleep until the store looks different from the last spl_gpu_sync, or timeout_ms passes.  Replaces a
+ * watcher's splinter_event_bus_open + splinter_event_bus_wait loop (splinter.c:1002-1033): the owner's
+ * eventfd (H->event_bus.owner_fd / owner_pid, splinter.h:144-148) is duplicated into this process (dup in
+ * the owner itself, pidfd_getfd elsewhere) and polled; H->epoch (splinter.h:186) is the gate.  Because
+ * only the process that ran splinter_event_bus_init writes that fd (splinter.c:929-939: g_event_fd is
+ * per process) the wait also re-reads H->epoch every few milliseconds, so writes by other processes are
+ * noticed without the bus, and a store with no bus at all degrades to that timed check.
+ * Returns 1 = H->epoch moved since the last sync (call spl_gpu_sync), 0 = timed out unchanged,
+ * <0 = error.  Like the reference's wait it consumes the eventfd count it wakes up on.
+ * splinter_unset moves neither H->epoch nor the bus (splinter.c:326-362): sweep on a timer as well. */
+int spl_gpu_wait(spl_gpu_ctx *ctx, uint32_t timeout_ms);
+
 /* dense contexts: copy rows [first_row, first_row+n_rows) from host arrays.  flags bits are
  * SPL_ROW_*; bloom/flags/epoch may be NULL (-> 0 / all candidate bits / 2). */
 #define SPL_ROW_LIST 0x01u /* splinter_list candidate:      hash!=0 && val_len>0 && epoch!=0 && key[0] */

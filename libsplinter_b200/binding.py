@@ -18,7 +18,7 @@ LIB_PATH = _HERE / "libsplinter_gpu.so"
 # symbols include/splinter_gpu.h declares; tests check every one is exported
 ABI_SYMBOLS = [
     "spl_gpu_attach", "spl_gpu_attach_image", "spl_gpu_open_dense", "spl_gpu_detach", "spl_gpu_get_info",
-    "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
+    "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_wait", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
     "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device",
     "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
 ]
@@ -88,6 +88,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_last_error.argtypes = []
     lib.spl_gpu_sync.restype = C.c_int
     lib.spl_gpu_sync.argtypes = [vp, C.POINTER(SyncStats)]
+    lib.spl_gpu_wait.restype = C.c_int
+    lib.spl_gpu_wait.argtypes = [vp, u32]
     lib.spl_gpu_dense_upload.restype = C.c_int
     lib.spl_gpu_dense_upload.argtypes = [vp, u64, u64, vp, vp, vp, vp]
     lib.spl_gpu_dense_fill_synthetic.restype = C.c_int
@@ -137,6 +139,8 @@ class Mirror:
             raise SplinterGpuError(self._lib.spl_gpu_last_error().decode() or "attach failed")
         self._h = C.c_void_p(handle)
         self._keep = None
+        i = self.info()                 # geometry is fixed for the life of a context
+        self._dim, self._slot_count = int(i.dim), int(i.slot_count)
 
     # ---- constructors ----
     @classmethod
@@ -185,6 +189,13 @@ class Mirror:
         self._check(self._lib.spl_gpu_get_info(self._h, C.byref(i)))
         return i
 
+    def wait(self, timeout_ms: int) -> bool:
+        """True when the store moved since the last sync (event bus / H->epoch), False on timeout."""
+        rc = self._lib.spl_gpu_wait(self._h, int(timeout_ms))
+        if rc < 0:
+            self._check(rc)
+        return rc == 1
+
     def sync(self) -> SyncStats:
         s = SyncStats()
         self._check(self._lib.spl_gpu_sync(self._h, C.byref(s)))
@@ -212,7 +223,7 @@ class Mirror:
 
     def params(self, nq, k, order=ORDER_COSINE, mode=MODE_AUTO, bloom_mask=0, min_similarity=0.0,
                max_distance=0.0, exclude_slot=NO_SLOT) -> SearchParams:
-        return SearchParams(C.sizeof(SearchParams), nq, self.info().dim, k, order, mode, bloom_mask,
+        return SearchParams(C.sizeof(SearchParams), nq, self._dim, k, order, mode, bloom_mask,
                             min_similarity, max_distance, exclude_slot, 0)
 
     def search(self, q, k, out_stride=None, **kw):
@@ -223,10 +234,11 @@ class Mirror:
         nq = q.shape[0]
         p = self.params(nq, k, **kw)
         p.dim = q.shape[1]  # a wrong dimension must be rejected by the library, not papered over here
-        stride = out_stride if out_stride is not None else (k if k > 0 else int(self.info().slot_count))
+        stride = out_stride if out_stride is not None else (k if k > 0 else self._slot_count)
         out = np.zeros((nq, stride), RESULT_DTYPE)
         counts = np.zeros(nq, np.uint32)
-        self._check(self._lib.spl_gpu_search(self._h, C.byref(p), _ptr(q), _ptr(out), stride, _ptr(counts)))
+        self._check(self._lib.spl_gpu_search(self._h, C.byref(p), q.ctypes.data, out.ctypes.data, stride,
+                                             counts.ctypes.data))
         return out, counts
 
     def search_device(self, p: SearchParams, d_q: int, d_out: int, out_stride: int, d_counts: int, stream: int = 0):

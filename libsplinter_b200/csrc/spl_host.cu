@@ -16,8 +16,12 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <poll.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
+#include <sys/syscall.h>
+#include <sys/uio.h>
+#include <time.h>
 #include <unistd.h>
 
 #include <atomic>
@@ -38,6 +42,7 @@ namespace layout {
 constexpr uint32_t kMagic = 0x534C4E54u, kVersion = 4u;
 constexpr size_t kHeaderSize = 5440, kSlotMeta = 128;
 constexpr size_t H_MAGIC = 0, H_VERSION = 4, H_SLOTS = 8, H_MAXVAL = 12, H_EPOCH = 16;
+constexpr size_t H_BUS_OWNER_FD = 4352, H_BUS_OWNER_PID = 4356;  // H->event_bus.owner_fd / owner_pid (splinter.h:144-148)
 constexpr size_t S_HASH = 0, S_EPOCH = 8, S_VAL_LEN = 20, S_BLOOM = 56, S_KEY = 64, S_EMBED = 128;
 }  // namespace layout
 
@@ -93,6 +98,8 @@ struct spl_gpu_ctx {
     std::vector<uint64_t> c_fp;     // fingerprint of the mirrored row's first 64 bytes (epoch-ABA detector)
     uint64_t c_header_epoch = 0;
     bool first_sync = true;
+    int bus_fd = -1;               // this process's duplicate of the owner's eventfd (spl_gpu_wait)
+    int32_t bus_owner_pid = 0, bus_owner_fd = -1;
     std::atomic<uint64_t> generation{0};
     // per-sync-thread staging (2 row buffers + 2 meta buffers each)
     std::vector<StageBuf> stage;
@@ -166,8 +173,8 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     const char *impl = getenv("SPL_GPU_SCAN_IMPL");  // developer knob: "ldg" forces the register-path kernel
     c->force_ldg = impl && strcmp(impl, "ldg") == 0;
     if (getenv("SPL_GPU_DEBUG_TIMELINE")) {
-        CUDA_TRY(cudaMalloc((void **)&c->d_dbg, 1024 * 4 * sizeof(unsigned long long)));
-        CUDA_TRY(cudaMemset(c->d_dbg, 0, 1024 * 4 * sizeof(unsigned long long)));
+        CUDA_TRY(cudaMalloc((void **)&c->d_dbg, 1024 * 8 * sizeof(unsigned long long)));
+        CUDA_TRY(cudaMemset(c->d_dbg, 0, 1024 * 8 * sizeof(unsigned long long)));
     }
     return 0;
 }
@@ -258,6 +265,7 @@ static void destroy(spl_gpu_ctx *c) {
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->bus_fd >= 0) close(c->bus_fd);
     if (c->own_map && c->base) munmap((void *)c->base, c->map_size);
     delete c;
 }
@@ -368,7 +376,7 @@ extern "C" int spl_gpu_debug_timeline(spl_gpu_ctx *c, unsigned long long *out, i
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     int n = max_ctas < c->sm_count ? max_ctas : c->sm_count;
-    cudaMemcpy(out, c->d_dbg, (size_t)n * 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaMemcpy(out, c->d_dbg, (size_t)n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     return n;
 }
 
@@ -465,7 +473,15 @@ static bool row_is_zero(const uint8_t *p, size_t bytes) {
     return acc == 0;
 }
 
-static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, bool header_moved, SyncCounters *scp) {
+// Sweep threads pull fixed-size slot ranges from a shared counter: on a host whose cores are also running
+// the store's writers a static split would wait for whichever thread shares a core with one of them.
+static inline uint64_t sweep_chunk(const spl_gpu_ctx *c) {
+    const uint64_t per = c->n / (8ull * (c->sync_threads ? c->sync_threads : 1));
+    return per < 256 ? 256 : (per > 4096 ? 4096 : per);
+}
+
+static void sync_worker(spl_gpu_ctx *c, unsigned tid, std::atomic<uint64_t> *next_chunk, bool header_moved,
+                        SyncCounters *scp) {
     using namespace layout;
     SyncCounters &sc = *scp;
     cudaSetDevice(c->device);
@@ -473,6 +489,11 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, 
     int rcur = 0, mcur = 0;
     if (acquire_buf(rb[0]) || acquire_buf(mb[0])) { sc.err = 1; return; }
     const size_t row_bytes = (size_t)c->dim * 4;
+    const uint64_t chunk = sweep_chunk(c);
+    for (;;) {
+    const uint64_t lo = next_chunk->fetch_add(1, std::memory_order_relaxed) * chunk;
+    if (lo >= c->n) break;
+    const uint64_t hi = lo + chunk < c->n ? lo + chunk : c->n;
     for (uint64_t r = lo; r < hi; r++) {
         const uint8_t *sl = c->base + kHeaderSize + (c->slot_begin + r) * c->slot_size;
         const uint64_t h = ld_acq64(sl + S_HASH);
@@ -560,6 +581,7 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, uint64_t lo, uint64_t hi, 
             if (acquire_buf(rb[rcur])) { sc.err = 1; return; }
         }
     }
+    }
     if (flush_buf(c, rb[rcur], true, sc) || flush_buf(c, mb[mcur], false, sc)) sc.err = 1;
 }
 
@@ -574,13 +596,8 @@ extern "C" int spl_gpu_sync(spl_gpu_ctx *c, spl_gpu_sync_stats *stats) {
     SyncCounters sc;
     const unsigned T = c->sync_threads;
     std::vector<std::thread> th;
-    const uint64_t per = (c->n + T - 1) / T;
-    for (unsigned t = 0; t < T; t++) {
-        uint64_t lo = per * t, hi = lo + per;
-        if (lo > c->n) lo = c->n;
-        if (hi > c->n) hi = c->n;
-        th.emplace_back(sync_worker, c, t, lo, hi, header_moved, &sc);
-    }
+    std::atomic<uint64_t> next_chunk{0};
+    for (unsigned t = 0; t < T; t++) th.emplace_back(sync_worker, c, t, &next_chunk, header_moved, &sc);
     for (auto &x : th) x.join();
     auto t1 = std::chrono::steady_clock::now();
     if (sc.err.load()) return fail(-1, EIO, "sync worker failed while staging rows to the device");
@@ -605,6 +622,63 @@ extern "C" int spl_gpu_sync(spl_gpu_ctx *c, spl_gpu_sync_stats *stats) {
         stats->header_epoch = hdr_epoch;
     }
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// wake-up: the reference's event bus as a hint, H->epoch as the gate
+// ------------------------------------------------------------------------------------------------
+static void bus_attach(spl_gpu_ctx *c) {
+    using namespace layout;
+    const int32_t fd = (int32_t)ld_acq32(c->base + H_BUS_OWNER_FD), pid = (int32_t)ld_acq32(c->base + H_BUS_OWNER_PID);
+    if (fd == c->bus_owner_fd && pid == c->bus_owner_pid && c->bus_fd >= 0) return;  // same bus as before
+    if (c->bus_fd >= 0) { close(c->bus_fd); c->bus_fd = -1; }
+    c->bus_owner_fd = fd; c->bus_owner_pid = pid;
+    if (fd < 0 || pid <= 0) return;  // splinter_event_bus_init never ran (splinter.c:991-999): timed checks only
+    if ((pid_t)pid == getpid()) { c->bus_fd = dup(fd); return; }  // splinter.c:1009-1010
+#if defined(SYS_pidfd_open) && defined(SYS_pidfd_getfd)
+    const int pidfd = (int)syscall(SYS_pidfd_open, (pid_t)pid, 0);  // splinter.c:1013-1018
+    if (pidfd < 0) return;
+    c->bus_fd = (int)syscall(SYS_pidfd_getfd, pidfd, fd, 0);
+    close(pidfd);
+    if (c->bus_fd >= 0) {  // the owner may have died and its pid/fd numbers been reused: accept eventfds only
+        char link[64], target[64];
+        snprintf(link, sizeof link, "/proc/self/fd/%d", c->bus_fd);
+        const ssize_t n = readlink(link, target, sizeof target - 1);
+        if (n <= 0 || strncmp(target, "anon_inode:[eventfd", 19) != 0) { close(c->bus_fd); c->bus_fd = -1; }
+    }
+#endif
+}
+
+extern "C" int spl_gpu_wait(spl_gpu_ctx *c, uint32_t timeout_ms) {
+    using namespace layout;
+    if (!c) return fail(-2, EINVAL, "null context");
+    if (c->dense) return fail(-2, EINVAL, "dense contexts have no backing store to wait on");
+    const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
+    constexpr int kSliceMs = 2;  // how stale a write by a process that does not own the bus can get
+    for (;;) {
+        if (ld_acq64(c->base + H_EPOCH) != c->c_header_epoch || c->first_sync) return 1;
+        const auto now = std::chrono::steady_clock::now();
+        if (now >= deadline) return 0;
+        long left = (long)std::chrono::duration_cast<std::chrono::milliseconds>(deadline - now).count();
+        const int slice = left < kSliceMs ? (int)(left > 0 ? left : 1) : kSliceMs;
+        bus_attach(c);
+        if (c->bus_fd >= 0) {
+            struct pollfd pfd = { c->bus_fd, POLLIN, 0 };
+            const int pr = poll(&pfd, 1, slice);
+            if (pr > 0 && (pfd.revents & POLLIN)) {
+                // consume the count like splinter_event_bus_wait does (splinter.c:1032), but without blocking if
+                // another watcher drained it first and without touching the shared O_NONBLOCK file flag
+                uint64_t v;
+                struct iovec iov = { &v, sizeof v };
+                if (preadv2(c->bus_fd, &iov, 1, -1, RWF_NOWAIT) < 0 && errno != EAGAIN) { close(c->bus_fd); c->bus_fd = -1; }
+            } else if (pr > 0) {  // POLLERR / POLLHUP: the bus is gone
+                close(c->bus_fd); c->bus_fd = -1;
+            }
+        } else {
+            struct timespec ts = { 0, slice * 1000000L };
+            nanosleep(&ts, nullptr);
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1019,13 +1093,28 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             const uint32_t nq = (p->nq - q0 < c->q_cap) ? p->nq - q0 : c->q_cap;
             spl_gpu_search_params pp = *p;
             pp.nq = nq;
+            static const bool probe = getenv("SPL_GPU_DEBUG_E2E") != nullptr;
+            static double acc[4]; static int calls;
+            auto T0 = std::chrono::steady_clock::now();
             memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
             CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
+            auto T1 = std::chrono::steady_clock::now();
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
             memset(c->h_total + q0, 0, nq * sizeof(uint32_t));  // mapped memory; ordered before the launch below
             if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream, c->m_total + q0))) return rc;
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+            auto T2 = std::chrono::steady_clock::now();
             CUDA_TRY(cudaStreamSynchronize(c->stream));
+            auto T3 = std::chrono::steady_clock::now();
+            if (probe) {
+                acc[0] += std::chrono::duration<double, std::micro>(T1 - T0).count();
+                acc[1] += std::chrono::duration<double, std::micro>(T2 - T1).count();
+                acc[2] += std::chrono::duration<double, std::micro>(T3 - T2).count();
+                if (++calls % 200 == 0) {
+                    fprintf(stderr, "[e2e probe] memcpy call %.1f us, launch call %.1f us, sync wait %.1f us\n", acc[0] / 200, acc[1] / 200, acc[2] / 200);
+                    acc[0] = acc[1] = acc[2] = 0;
+                }
+            }
             if (c->timing) {
                 float ms = 0.f;
                 CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));

@@ -13,6 +13,13 @@
 
 namespace spl {
 
+__device__ __forceinline__ unsigned long long gtime_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+
 __host__ __device__ inline uint32_t next_pow2(uint32_t x) {
     uint32_t p = 1;
     while (p < x) p <<= 1;
@@ -97,6 +104,7 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
     __shared__ uint64_t xk[NW * 32];
     __shared__ uint32_t xi[NW * 32];
     cta_tree_merge32<NW>(key, idx, xk, xi);
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 4] = gtime_ns();
     if (warp == 0 && lane < k) {
         Cand c; c.key = key; c.idx = idx; c.pad = 0;
         a.cta_cands[(size_t)blockIdx.x * k + lane] = c;
@@ -108,6 +116,7 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
         *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
     }
     __syncthreads();
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 5] = gtime_ns();
     if (*s_flag == 0) return;
     // 3. last CTA: each warp folds a strided subset of the gridDim.x published (sorted) lists
     __threadfence();
@@ -131,7 +140,9 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
                 if (c0 + j * NW < gridDim.x) warp_merge32(key, idx, bk[j], bi[j], lane);
         }
     }
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 6] = gtime_ns();
     cta_tree_merge32<NW>(key, idx, xk, xi);
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 7] = gtime_ns();
     if (warp == 0) {
         if (lane == 0) {
             if (a.total) *a.total = *reinterpret_cast<volatile uint32_t *>(&a.counters[2]);

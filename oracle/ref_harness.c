@@ -13,6 +13,7 @@
  * may load it.
  */
 #include <pthread.h>
+#include <stddef.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -54,6 +55,10 @@ int ref_embed_dim(void) { return SPLINTER_EMBED_DIM; }
 size_t ref_sizeof_slot(void) { return sizeof(struct splinter_slot); }
 size_t ref_sizeof_header(void) { return sizeof(struct splinter_header); }
 size_t ref_sizeof_result(void) { return sizeof(search_result_t); }
+/* where a watcher finds the owner's eventfd (splinter.h:144-148, :210) and the epoch gate (:186) */
+size_t ref_offsetof_bus_owner_fd(void) { return offsetof(struct splinter_header, event_bus) + offsetof(struct splinter_event_bus, owner_fd); }
+size_t ref_offsetof_bus_owner_pid(void) { return offsetof(struct splinter_header, event_bus) + offsetof(struct splinter_event_bus, owner_pid); }
+size_t ref_offsetof_header_epoch(void) { return offsetof(struct splinter_header, epoch); }
 
 /* Run the real command in-process (caller must have splinter_open()ed the
  * store through the same libsplinter.so).  Output goes to stdout as usual. */

@@ -129,6 +129,7 @@ def ref_store() -> C.CDLL:
         lib.splinter_bump_slot.argtypes = [C.c_char_p]
         lib.splinter_enumerate_matches.restype = None
         lib.splinter_list.restype = C.c_int
+        lib.splinter_event_bus_init.restype = C.c_int
         _ref_store = lib
     return _ref_store
 
@@ -153,6 +154,8 @@ def ref_search() -> C.CDLL:
         lib.ref_sizeof_header.restype = C.c_size_t
         lib.ref_sizeof_result.restype = C.c_size_t
         lib.ref_embed_dim.restype = C.c_int
+        for f in ("ref_offsetof_bus_owner_fd", "ref_offsetof_bus_owner_pid", "ref_offsetof_header_epoch"):
+            getattr(lib, f).restype = C.c_size_t
         _ref_search = lib
     return _ref_search
 

@@ -267,3 +267,12 @@ def test_real_search_command_end_to_end(ref_store_name, tmp_path):
             assert row["key"] == key
             assert row["similarity"] == pytest.approx(float(g["similarity"]), abs=5.1e-5)
             assert row["distance"] == pytest.approx(float(g["distance"]), abs=5.1e-5)
+
+
+def test_event_bus_and_epoch_offsets_match_the_reference_header():
+    """spl_gpu_wait reads H->event_bus.owner_fd / owner_pid and H->epoch straight out of the mapping
+    (libsplinter_b200/csrc/spl_host.cu: layout::H_BUS_OWNER_FD / H_BUS_OWNER_PID / H_EPOCH)."""
+    rs = support.ref_search()
+    assert rs.ref_offsetof_bus_owner_fd() == 4352
+    assert rs.ref_offsetof_bus_owner_pid() == 4356
+    assert rs.ref_offsetof_header_epoch() == 16
