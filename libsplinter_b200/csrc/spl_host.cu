@@ -141,6 +141,7 @@ struct spl_gpu_ctx {
     std::mutex mu;  // serialises enqueueing on `stream` and the scratch above
     std::atomic<uint64_t> launches{0};
     bool force_ldg = false;
+    bool no_multi = false;  // developer knob SPL_GPU_SCAN_MULTI=0: one query per launch even for small batches
     unsigned long long *d_dbg = nullptr;  // SPL_GPU_DEBUG_TIMELINE=1: per-CTA timestamps of the last scan
     bool timing = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -172,6 +173,8 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     CUDA_TRY(batch_prepare());
     const char *impl = getenv("SPL_GPU_SCAN_IMPL");  // developer knob: "ldg" forces the register-path kernel
     c->force_ldg = impl && strcmp(impl, "ldg") == 0;
+    const char *multi = getenv("SPL_GPU_SCAN_MULTI");
+    c->no_multi = multi && strcmp(multi, "0") == 0;
     if (getenv("SPL_GPU_DEBUG_TIMELINE")) {
         CUDA_TRY(cudaMalloc((void **)&c->d_dbg, 1024 * 8 * sizeof(unsigned long long)));
         CUDA_TRY(cudaMemset(c->d_dbg, 0, 1024 * 8 * sizeof(unsigned long long)));
@@ -772,20 +775,33 @@ static void fill_args(const spl_gpu_ctx *c, const spl_gpu_search_params *p, Scan
 
 // enqueue one fused top-k scan per query (k in 1..KMAX_FUSED); caller holds c->mu
 static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, spl_gpu_result *d_out,
-                         uint32_t out_stride, uint32_t *d_counts, cudaStream_t s, uint32_t *d_totals = nullptr) {
+                         uint32_t out_stride, uint32_t *d_counts, cudaStream_t s, uint32_t *d_totals = nullptr,
+                         uint32_t count_stride = 1) {
     uint32_t mode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
     if (mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "mode %u is not available for this query shape", mode);
     ScanArgs a;
     fill_args(c, p, a);
     a.k = p->k;
-    for (uint32_t qi = 0; qi < p->nq; qi++) {
+    const bool tma = !c->force_ldg && scan_tma_supported(a.dim, a.k);
+    a.out_stride = out_stride;
+    a.count_stride = count_stride;
+    for (uint32_t qi = 0; qi < p->nq;) {
+        // small batches: 4 (then 2) queries share one pass over the store, so each row read from HBM is scored
+        // for all of them; the rest go one per launch
+        uint32_t g = 1;
+        if (tma && !c->no_multi) {
+            if (p->nq - qi >= 4 && scan_tma_multi_supported(a.dim, a.k, 4)) g = 4;
+            else if (p->nq - qi >= 2 && scan_tma_multi_supported(a.dim, a.k, 2)) g = 2;
+        }
+        a.nq = g;
         a.q = d_q + (size_t)qi * c->dim;
         a.out = d_out + (size_t)qi * out_stride;
-        a.out_count = d_counts + qi;
+        a.out_count = d_counts + (size_t)qi * count_stride;
         a.total = d_totals ? d_totals + qi : nullptr;
-        if (!c->force_ldg && scan_tma_supported(a.dim, a.k)) CUDA_TRY(launch_scan_tma(a, c->sm_count, s));
+        if (tma) CUDA_TRY(launch_scan_tma(a, c->sm_count, s));
         else CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
         c->launches++;
+        qi += g;
     }
     return 0;
 }
@@ -828,14 +844,18 @@ static int enqueue_exact(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
     spl_gpu_search_params fastp = *p;
     fastp.mode = SPL_MODE_FAST;
     fastp.k = kprime;
-    fastp.nq = 1;
+    fastp.nq = nq;
     if (p->min_similarity > 0.f) fastp.min_similarity = p->min_similarity - kExactSimBound;
     if (p->max_distance > 0.f) fastp.max_distance = p->max_distance * (1.f + kExactDistRel);
+    {   // candidate scans for all queries (small batches share passes), each into its own scratch slice
+        static_assert(kExactPerQuery % sizeof(spl_gpu_result) == 0, "slices must be a whole number of records apart");
+        const ExactSlices x0 = exact_slices(c, 0);
+        int rc = enqueue_fused(c, &fastp, d_q, x0.cand, (uint32_t)(kExactPerQuery / sizeof(spl_gpu_result)), x0.cand_count, s,
+                               d_totals, (uint32_t)(kExactPerQuery / sizeof(uint32_t)));
+        if (rc) return rc;
+    }
     for (uint32_t qi = 0; qi < nq; qi++) {
         const ExactSlices x = exact_slices(c, qi);
-        int rc = enqueue_fused(c, &fastp, d_q + (size_t)qi * c->dim, x.cand, kprime, x.cand_count, s,
-                               d_totals ? d_totals + qi : nullptr);
-        if (rc) return rc;
         ExactArgs a;
         memset(&a, 0, sizeof a);
         a.E = c->m.E; a.q = d_q + (size_t)qi * c->dim; a.dim = c->dim; a.order = p->order; a.k = p->k; a.kprime = kprime;

@@ -28,6 +28,9 @@ struct ScanArgs {
     uint64_t *keys_out;
     uint32_t *total;         // nullable: where the LAST CTA stores the number of rows that passed predicate and
                              // thresholds (accumulated in counters[2]; may point to mapped host memory)
+    uint32_t nq;             // TMA kernel: queries scored per pass (0/1, 2 or 4); q holds nq vectors back to back,
+    uint32_t out_stride;     //   query i writes out + i*out_stride, out_count[i*count_stride], total[i] (counters[2+i])
+    uint32_t count_stride;
     uint32_t chunk_groups;   // TMA kernel: 32-slot groups handed out per work-counter increment (1..8)
     // developer timeline (nullable): per CTA {start, producers done, consumers done, end} in ns
     unsigned long long *dbg;
@@ -58,6 +61,7 @@ int scan_fast_ctas_per_sm(uint32_t dim, uint32_t k);
 
 // TMA-staged variant (spl_scan_tma.cu): one persistent CTA per SM
 bool scan_tma_supported(uint32_t dim, uint32_t k);
+bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq);
 cudaError_t scan_tma_prepare();
 cudaError_t launch_scan_tma(const ScanArgs &a, int grid, cudaStream_t stream);
 

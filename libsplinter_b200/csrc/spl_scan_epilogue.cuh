@@ -162,6 +162,107 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
     }
 }
 
+// ---- small-batch scans: NQ queries, each with NW per-warp lists of k <= 32 entries ---------------------
+// Lists of (query qi, warp w) sit at skeys/sidx[(qi*NW + w) * k]; xk/xi is an exchange buffer of NQ*NW*32
+// entries (the idle row ring).  All NQ merges share the same barriers.  Query qi writes a.out + qi*out_stride,
+// a.out_count[qi], a.total[qi]; its survivor count was accumulated in counters[2 + qi].
+template <int NW, int NQ>
+__device__ __forceinline__ void tree_merge32_multi(uint64_t (&key)[NQ], uint32_t (&idx)[NQ], uint64_t *xk, uint32_t *xi) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int step = 1; step < NW; step <<= 1) {
+        if (warp < NW && (warp & (2 * step - 1)) == step) {
+#pragma unroll
+            for (int qi = 0; qi < NQ; qi++) { xk[(qi * NW + warp) * 32 + lane] = key[qi]; xi[(qi * NW + warp) * 32 + lane] = idx[qi]; }
+        }
+        __syncthreads();
+        if (warp < NW && (warp & (2 * step - 1)) == 0 && warp + step < NW) {
+#pragma unroll
+            for (int qi = 0; qi < NQ; qi++)
+                warp_merge32(key[qi], idx[qi], xk[(qi * NW + warp + step) * 32 + lane], xi[(qi * NW + warp + step) * 32 + lane], lane);
+        }
+        // no second barrier: a region written at one level is never written again at a later one
+    }
+}
+
+template <int NW, int NQ>
+__device__ __forceinline__ void scan_epilogue_small_multi(const ScanArgs &a, const uint64_t *skeys, const uint32_t *sidx,
+                                                          uint64_t *xk, uint32_t *xi, uint32_t *s_flag) {
+    const uint32_t k = a.k, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();  // lists final, ring idle
+    uint64_t key[NQ]; uint32_t idx[NQ];
+#pragma unroll
+    for (int qi = 0; qi < NQ; qi++) {
+        key[qi] = kKeySentinel; idx[qi] = kIdxSentinel;
+        if (warp < NW && lane < k) { key[qi] = skeys[(qi * NW + warp) * k + lane]; idx[qi] = sidx[(qi * NW + warp) * k + lane]; }
+        if (warp < NW) warp_sort32(key[qi], idx[qi], lane);
+    }
+    tree_merge32_multi<NW, NQ>(key, idx, xk, xi);
+    if (warp == 0 && lane < k) {
+#pragma unroll
+        for (int qi = 0; qi < NQ; qi++) {
+            Cand c; c.key = key[qi]; c.idx = idx[qi]; c.pad = 0;
+            a.cta_cands[((size_t)qi * gridDim.x + blockIdx.x) * k + lane] = c;
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
+        *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (*s_flag == 0) return;
+    // last CTA: fold every CTA's published list, query by query
+    __threadfence();
+#pragma unroll
+    for (int qi = 0; qi < NQ; qi++) {
+        key[qi] = kKeySentinel; idx[qi] = kIdxSentinel;
+        if (warp < NW) {
+            constexpr int kBatch = 10;
+            const Cand *lists = a.cta_cands + (size_t)qi * gridDim.x * k;
+            for (uint32_t c0 = warp; c0 < gridDim.x; c0 += NW * kBatch) {
+                uint64_t bk[kBatch]; uint32_t bi[kBatch];
+#pragma unroll
+                for (int j = 0; j < kBatch; j++) {
+                    const uint32_t c = c0 + j * NW;
+                    bk[j] = kKeySentinel; bi[j] = kIdxSentinel;
+                    if (c < gridDim.x && lane < k) {
+                        const int4 raw = __ldcg(reinterpret_cast<const int4 *>(lists + (size_t)c * k + lane));
+                        bk[j] = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
+                        bi[j] = (uint32_t)raw.z;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < kBatch; j++)
+                    if (c0 + j * NW < gridDim.x) warp_merge32(key[qi], idx[qi], bk[j], bi[j], lane);
+            }
+        }
+    }
+    tree_merge32_multi<NW, NQ>(key, idx, xk, xi);
+    if (warp == 0) {
+#pragma unroll
+        for (int qi = 0; qi < NQ; qi++) {
+            const unsigned valid = __ballot_sync(0xffffffffu, lane < k && idx[qi] != kIdxSentinel);
+            if (lane == 0) {
+                a.out_count[(size_t)qi * a.count_stride] = __popc(valid);
+                if (a.total) a.total[qi] = *reinterpret_cast<volatile uint32_t *>(&a.counters[2 + qi]);
+            }
+            if (lane < k && idx[qi] != kIdxSentinel) {
+                spl_gpu_result r;
+                split_key(a.order, key[qi], r.similarity, r.distance);
+                r.slot_idx = (uint32_t)(a.row0 + idx[qi]);
+                r.has_embedding = (a.flags[idx[qi]] & SPL_ROW_EMB) ? 1u : 0u;
+                r.epoch = a.epoch[idx[qi]];
+                r.bloom = a.bloom[idx[qi]];
+                a.out[(size_t)qi * a.out_stride + lane] = r;
+            }
+        }
+        __syncwarp();
+        if (lane < 2 + NQ) a.counters[lane] = 0;
+    }
+}
+
 // workspace the final merge may use: `ws_entries` (power of two, >= 2*k) entries at ws_keys/ws_idx
 template <int NW>
 __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys, uint32_t *sidx, uint64_t *ws_keys,

@@ -18,6 +18,8 @@
 // compute warps are doing -- what an HBM-bound gather of 3 KB rows needs.
 #include <float.h>
 
+#include <type_traits>
+
 #include "spl_scan.cuh"
 #include "spl_scan_epilogue.cuh"
 
@@ -59,6 +61,19 @@ __device__ __forceinline__ void wait_gen(uint32_t addr, uint32_t gen) {
         asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
     } while (v != gen);
 }
+// producer flavour: when the consumers are the slower side (small-batch scans) 128 producer lanes spinning on
+// shared memory would steal load/store bandwidth and issue slots from them, so back off between polls
+__device__ __forceinline__ void wait_gen_backoff(uint32_t addr, uint32_t gen) {
+    uint32_t v;
+    int spins = 0;
+    for (;;) {
+        asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+        if (v == gen) return;
+        // The ring holds ~4x the bytes the HBM latency-bandwidth product needs, so a refill that comes a
+        // fraction of a microsecond late costs nothing, while a tight poll costs the consumers issue slots.
+        if (++spins > 2) __nanosleep(spins > 8 ? 500 : 200);
+    }
+}
 __device__ __forceinline__ void publish_gen(uint32_t addr, uint32_t gen) {
     asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(addr), "r"(gen) : "memory");
 }
@@ -72,19 +87,46 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+// Packed fp32 pairs (FFMA2, sm_100): one instruction does the (x, y) or (z, w) half of a float4.  Every sum below
+// is kept as two partial sums (x/z components, y/w components) that are added once at the end -- in the single-
+// and the multi-query loop alike, so both produce the same bits.
+__device__ __forceinline__ float2 lo2(const float4 &v) { return make_float2(v.x, v.y); }
+__device__ __forceinline__ float2 hi2(const float4 &v) { return make_float2(v.z, v.w); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a); }  // a - b, one rounding
+// one float4 of query q against one float4 of row e: dot += q*e, ss += (q-e)^2
+__device__ __forceinline__ void score4(const float4 &q, const float4 &e, float2 &dot, float2 &ss) {
+    dot = fma2(lo2(q), lo2(e), dot);
+    float2 t = sub2(lo2(q), lo2(e));
+    ss = fma2(t, t, ss);
+    dot = fma2(hi2(q), hi2(e), dot);
+    t = sub2(hi2(q), hi2(e));
+    ss = fma2(t, t, ss);
+}
+__device__ __forceinline__ void norm4(const float4 &e, float2 &n) {
+    n = fma2(lo2(e), lo2(e), n);
+    n = fma2(hi2(e), hi2(e), n);
+}
+
 struct TmaLayout {
-    uint32_t pairs, row_bytes, rows_off, full_off, empty_off, meta_off, clist_off, total;
+    uint32_t pairs, row_bytes, rows_off, full_off, empty_off, meta_off, clist_off, state_off, q_off, list_entries, total;
 };
 
-__host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k) {
+// nq > 1 (small-batch scan): nq * kConsumers lists of k entries, their bookkeeping words and the nq
+// queries themselves live in shared memory as well; the ring gets what is left.
+__host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32_t nq = 1) {
     TmaLayout L;
     L.row_bytes = dim * 4;
-    const uint32_t topk = (uint32_t)scan_topk_smem(k, kConsumers);
+    L.list_entries = nq == 1 ? scan_topk_entries(k, kConsumers) : nq * kConsumers * k;
+    const uint32_t topk = L.list_entries * 12u;                    // u64 keys[] then u32 idx[]
     L.full_off = (topk + 15u) & ~15u;                             // top-k lists sit at offset 0
     L.empty_off = L.full_off + kMaxPairs * 8;
     L.meta_off = L.empty_off + kMaxPairs * 8;                     // uint4 {row0, flags0, row1, flags1}
     L.clist_off = L.meta_off + kMaxPairs * 16;                    // per producer warp: 256 x {row, flags}
-    L.rows_off = (L.clist_off + kProducers * 256 * 8 + 127u) & ~127u;
+    L.state_off = L.clist_off + kProducers * 256 * 8;             // nq > 1: uint4 per (query, consumer warp)
+    L.q_off = L.state_off + (nq > 1 ? nq * kConsumers * 20u + 16u : 0u);  // + u32 survivors per list, |q|^2 per query
+                                                                  // nq > 1: the queries, fp32 [nq][dim], go here
+    L.rows_off = (L.q_off + (nq > 1 ? nq * L.row_bytes : 0u) + 127u) & ~127u;
     const uint32_t avail = kSmemBudget - 8192u - L.rows_off;      // 8 KB headroom for static smem
     const uint32_t p = avail / (2 * L.row_bytes);
     L.pairs = p > kMaxPairs ? kMaxPairs : p;
@@ -92,14 +134,14 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k) {
     return L;
 }
 
-template <int V>
+template <int V, int NQ>
 __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint32_t s_flag;
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const TmaLayout L = tma_layout(a.dim, a.k);
-    const uint32_t list_entries = scan_topk_entries(a.k, kConsumers);
+    const TmaLayout L = tma_layout(a.dim, a.k, NQ);
+    const uint32_t list_entries = L.list_entries;
     uint64_t *skeys = reinterpret_cast<uint64_t *>(smem);
     uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + list_entries);
     const uint32_t full0 = smem_u32(smem + L.full_off), empty0 = smem_u32(smem + L.empty_off);
@@ -113,6 +155,16 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     topk_lists_init(skeys, sidx, list_entries);
+    if constexpr (NQ > 1) {
+        uint4 *wstate = reinterpret_cast<uint4 *>(smem + L.state_off);
+        for (uint32_t i = threadIdx.x; i < NQ * kConsumers; i += blockDim.x) {
+            wstate[i] = make_uint4((uint32_t)kKeySentinel, (uint32_t)(kKeySentinel >> 32), kIdxSentinel, 0u);
+            reinterpret_cast<uint32_t *>(wstate + NQ * kConsumers)[i] = 0u;
+        }
+        float4 *sq4 = reinterpret_cast<float4 *>(smem + L.q_off);
+        const float4 *gq4 = reinterpret_cast<const float4 *>(a.q);
+        for (uint32_t i = threadIdx.x; i < NQ * (a.dim >> 2); i += blockDim.x) sq4[i] = gq4[i];
+    }
     __syncthreads();
 
     WarpTopK W;
@@ -190,7 +242,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                     const uint32_t bytes = prev_adj ? 0u : (next_adj ? 2 * RB : RB);
                     // every lane waits for the slot's previous round to be handed back before it touches
                     // the slot's metadata or rows
-                    wait_gen(empty0 + 8 * slot, gen);
+                    wait_gen_backoff(empty0 + 8 * slot, gen);
                     meta32[slot * 4 + sub * 2] = me.x;
                     meta32[slot * 4 + sub * 2 + 1] = me.y;
                     if (bytes) {
@@ -241,7 +293,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                 mbar_arrive(full0 + 8 * slot);
             }
         }
-    } else {
+    } else if constexpr (NQ == 1) {
         // ================================ consumers ================================
         const float4 *q4 = reinterpret_cast<const float4 *>(a.q);
         float4 qv[V];
@@ -292,19 +344,14 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
             if (lane == 0) publish_gen(empty0 + 8 * slot, gen + 1);  // both rows now live in registers
             slot += kConsumers;
             if (slot >= NP) { slot -= NP; gen++; }
-            float d0 = 0.f, e0 = 0.f, s0 = 0.f, d1 = 0.f, e1 = 0.f, s1 = 0.f;
+            float2 pd0 = make_float2(0.f, 0.f), pe0 = pd0, ps0 = pd0, pd1 = pd0, pe1 = pd0, ps1 = pd0;
 #pragma unroll
             for (int j = 0; j < V; j++) {
-                float t, u;
-                d0 = fmaf(qv[j].x, x[j].x, d0); e0 = fmaf(x[j].x, x[j].x, e0); t = qv[j].x - x[j].x; s0 = fmaf(t, t, s0);
-                d1 = fmaf(qv[j].x, y[j].x, d1); e1 = fmaf(y[j].x, y[j].x, e1); u = qv[j].x - y[j].x; s1 = fmaf(u, u, s1);
-                d0 = fmaf(qv[j].y, x[j].y, d0); e0 = fmaf(x[j].y, x[j].y, e0); t = qv[j].y - x[j].y; s0 = fmaf(t, t, s0);
-                d1 = fmaf(qv[j].y, y[j].y, d1); e1 = fmaf(y[j].y, y[j].y, e1); u = qv[j].y - y[j].y; s1 = fmaf(u, u, s1);
-                d0 = fmaf(qv[j].z, x[j].z, d0); e0 = fmaf(x[j].z, x[j].z, e0); t = qv[j].z - x[j].z; s0 = fmaf(t, t, s0);
-                d1 = fmaf(qv[j].z, y[j].z, d1); e1 = fmaf(y[j].z, y[j].z, e1); u = qv[j].z - y[j].z; s1 = fmaf(u, u, s1);
-                d0 = fmaf(qv[j].w, x[j].w, d0); e0 = fmaf(x[j].w, x[j].w, e0); t = qv[j].w - x[j].w; s0 = fmaf(t, t, s0);
-                d1 = fmaf(qv[j].w, y[j].w, d1); e1 = fmaf(y[j].w, y[j].w, e1); u = qv[j].w - y[j].w; s1 = fmaf(u, u, s1);
+                score4(qv[j], x[j], pd0, ps0); norm4(x[j], pe0);
+                score4(qv[j], y[j], pd1, ps1); norm4(y[j], pe1);
             }
+            float d0 = pd0.x + pd0.y, e0 = pe0.x + pe0.y, s0 = ps0.x + ps0.y;
+            float d1 = pd1.x + pd1.y, e1 = pe1.x + pe1.y, s1 = ps1.x + ps1.y;
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) {
                 d0 += __shfl_xor_sync(0xffffffffu, d0, off);
@@ -318,13 +365,145 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
             if (two) finish(mt.z, mt.w, d1, e1, s1);
         }
         if (a.total && lane == 0 && nsurv) atomicAdd(&a.counters[2], nsurv);
+    } else {
+        // ===================== consumers, NQ queries per pass over the store =====================
+        // The pair of rows sits in registers as before; the queries are streamed from shared memory, so every
+        // row byte fetched from HBM is scored NQ times.  The 4*NQ partial sums of a pair (dot and sum of squared
+        // differences, per row, per query) are reduced across the warp TRANSPOSED: each halving step swaps half
+        // of the values, so after five steps lane L holds the complete sum of value (L / TB) in 4*NQ + ~8
+        // shuffles instead of 5 per value -- in the same pairwise order as the plain butterfly, so the scores are
+        // bit-identical to the single-query kernel's.  Each (query, row) result is then scored, thresholded and
+        // tested against its list by its own lane, all 2*NQ of them at once; only an admitted candidate (rare
+        // once the lists have warmed up) takes a warp-wide detour.
+        constexpr int NV = 4 * NQ;        // value index = (query * 2 + row) * 2 + {0: dot, 1: sum (q-e)^2}
+        constexpr uint32_t TB = 32 / NV;  // lane L ends up holding value L / TB
+        const float4 *sq4 = reinterpret_cast<const float4 *>(smem + L.q_off) + lane;
+        uint4 *wstate = reinterpret_cast<uint4 *>(smem + L.state_off);
+        float *smaq = reinterpret_cast<float *>(reinterpret_cast<uint32_t *>(wstate + NQ * kConsumers) + NQ * kConsumers);
+        const uint32_t qstride4 = a.dim >> 2;
+#pragma unroll 1
+        for (int qi = 0; qi < NQ; qi++) {
+            float m = 0.f;
+#pragma unroll
+            for (int j = 0; j < V; j++) {
+                const float4 v = sq4[qi * qstride4 + 32 * j];
+                m = fmaf(v.x, v.x, m); m = fmaf(v.y, v.y, m); m = fmaf(v.z, v.z, m); m = fmaf(v.w, v.w, m);
+            }
+            m = warp_sum(m);
+            if (lane == 0) smaq[qi] = m;   // every consumer warp stores the same value
+        }
+        __syncwarp();
+        const uint32_t my_q = lane / (4 * TB), my_r = (lane / (2 * TB)) & 1u, my_t = (lane / TB) & 1u;
+        const bool active = (lane % (2 * TB)) == 0;        // one lane per (query, row)
+        const uint32_t group_mask = (uint32_t)((1ull << (4 * TB)) - 1ull) << (my_q * 4 * TB);
+        const float maq = smaq[my_q];
+        const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+        uint4 *my_state = wstate + my_q * kConsumers + warp;
+        uint32_t nsurv = 0;  // survivors of this lane's query
+        auto tsum = [&](auto &v, auto n_tag) -> float {      // transposed warp sum of v[N]
+            constexpr int N = decltype(n_tag)::value;
+            uint32_t width = 16;
+#pragma unroll
+            for (int n = N; n > 1; n >>= 1, width >>= 1) {
+                const bool hi = (lane & width) != 0;
+#pragma unroll
+                for (int i = 0; i < n / 2; i++) {
+                    const float send = hi ? v[i] : v[i + n / 2];
+                    const float keep = hi ? v[i + n / 2] : v[i];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, width);
+                }
+            }
+            float r = v[0];
+            for (; width > 0; width >>= 1) r += __shfl_xor_sync(0xffffffffu, r, width);
+            return r;
+        };
+        uint32_t slot = warp, gen = 0;
+        if (slot >= NP) { slot -= NP; gen++; }
+        for (;;) {
+            wait_gen(empty0 + 8 * slot, gen);   // see the single-query loop for why both waits are needed
+            mbar_wait(full0 + 8 * slot, gen & 1u);
+            const uint4 mt = meta[slot];
+            if (mt.x == kIdxSentinel) break;
+            const float4 *r0 = reinterpret_cast<const float4 *>(smem + L.rows_off + (size_t)slot * 2 * RB) + lane;
+            const float4 *r1 = reinterpret_cast<const float4 *>(reinterpret_cast<const unsigned char *>(r0) + RB);
+            const bool two = mt.z != kIdxSentinel;
+            float4 x[V], y[V];
+#pragma unroll
+            for (int j = 0; j < V; j++) x[j] = r0[32 * j];
+#pragma unroll
+            for (int j = 0; j < V; j++) y[j] = two ? r1[32 * j] : x[j];
+            __syncwarp();
+            if (lane == 0) publish_gen(empty0 + 8 * slot, gen + 1);
+            slot += kConsumers;
+            if (slot >= NP) { slot -= NP; gen++; }
+            float2 pe0 = make_float2(0.f, 0.f), pe1 = pe0;
+#pragma unroll
+            for (int j = 0; j < V; j++) { norm4(x[j], pe0); norm4(y[j], pe1); }
+            float ev[2] = { pe0.x + pe0.y, pe1.x + pe1.y };
+            float acc[NV];
+#pragma unroll
+            for (int qi = 0; qi < NQ; qi++) {
+                const float4 *qrow = sq4 + qi * qstride4;
+                float2 pd0 = make_float2(0.f, 0.f), ps0 = pd0, pd1 = pd0, ps1 = pd0;
+#pragma unroll
+                for (int j = 0; j < V; j++) {
+                    const float4 qv = qrow[32 * j];
+                    score4(qv, x[j], pd0, ps0);
+                    score4(qv, y[j], pd1, ps1);
+                }
+                acc[qi * 4 + 0] = pd0.x + pd0.y; acc[qi * 4 + 1] = ps0.x + ps0.y;
+                acc[qi * 4 + 2] = pd1.x + pd1.y; acc[qi * 4 + 3] = ps1.x + ps1.y;
+            }
+            const float etot = tsum(ev, std::integral_constant<int, 2>{});   // lanes 0-15: |row0|^2, 16-31: |row1|^2
+            const float tot = tsum(acc, std::integral_constant<int, NV>{});
+            const float other = __shfl_xor_sync(0xffffffffu, tot, TB);
+            const float dot = my_t ? other : tot, ss = my_t ? tot : other;
+            const float mb = __shfl_sync(0xffffffffu, etot, my_r << 4);
+            const uint32_t row = my_r ? mt.z : mt.x, f = my_r ? mt.w : mt.y;
+            bool pass = active && (my_r == 0 || two);
+            float sim, dist;
+            if (f & SPL_ROW_EMB) {
+                sim = cosine_from_sums(dot, maq, mb);
+                dist = __fsqrt_rn(ss);
+                if (a.min_sim > 0.f && sim < a.min_sim) pass = false;
+                if (a.max_dist > 0.f && dist > a.max_dist) pass = false;
+            } else {  // _search.c:388-393
+                if (thresholds) pass = false;
+                sim = 0.f; dist = FLT_MAX;
+            }
+            const uint64_t key = make_key(a.order, sim, dist);
+            nsurv += __popc(__ballot_sync(0xffffffffu, pass) & group_mask);
+            const uint4 st = *my_state;
+            const bool admit = pass && ((st.w & 0xffffu) < a.k || better(key, row, ((uint64_t)st.y << 32) | st.x, st.z));
+            unsigned m = __ballot_sync(0xffffffffu, admit);
+            while (m) {   // warp-uniform
+                const int l = __ffs(m) - 1;
+                m &= m - 1;
+                const uint64_t ckey = __shfl_sync(0xffffffffu, key, l);
+                const uint32_t crow = __shfl_sync(0xffffffffu, row, l);
+                const uint32_t cq = (uint32_t)l / (4 * TB);
+                uint4 *stp = wstate + cq * kConsumers + warp;
+                const uint4 cs = *stp;   // re-read: an earlier candidate of this pair may have moved the bound
+                WarpTopK T;
+                T.keys = skeys + (cq * kConsumers + warp) * a.k; T.idxs = sidx + (cq * kConsumers + warp) * a.k;
+                T.k = a.k; T.cnt = cs.w & 0xffffu; T.thr_pos = cs.w >> 16;
+                T.thr_key = ((uint64_t)cs.y << 32) | cs.x; T.thr_idx = cs.z;
+                if (T.admits(ckey, crow)) {
+                    T.insert(ckey, crow, lane);
+                    if (lane == 0) *stp = make_uint4((uint32_t)T.thr_key, (uint32_t)(T.thr_key >> 32), T.thr_idx, (T.thr_pos << 16) | T.cnt);
+                }
+                __syncwarp();
+            }
+        }
+        if (a.total && (lane % (4 * TB)) == 0 && nsurv) atomicAdd(&a.counters[2 + my_q], nsurv);
     }
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 2] = gtime();
     // the row ring is idle now: it becomes the workspace of the final cross-CTA merge
     uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
     uint64_t *ws_keys = reinterpret_cast<uint64_t *>(smem + L.rows_off);
     uint32_t *ws_idx = reinterpret_cast<uint32_t *>(ws_keys + ws_entries);
-    scan_epilogue<kConsumers>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
+    if constexpr (NQ == 1) scan_epilogue<kConsumers>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
+    else scan_epilogue_small_multi<kConsumers, NQ>(a, skeys, sidx, ws_keys, reinterpret_cast<uint32_t *>(ws_keys + NQ * kConsumers * 32), &s_flag);
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 3] = gtime();
 }
 
@@ -333,23 +512,48 @@ bool scan_tma_supported(uint32_t dim, uint32_t k) {
     return tma_layout(dim, k).pairs >= kMinPairs;
 }
 
-template <int V>
+// small-batch variant: nq in {2, 4} queries per pass, register/shuffle epilogue only (k <= 32)
+bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq) {
+    if (nq != 2 && nq != 4) return false;
+    if (k == 0 || k > 32 || !scan_tma_supported(dim, k)) return false;
+    const TmaLayout L = tma_layout(dim, k, nq);
+    return L.pairs >= kMinPairs && (size_t)nq * kConsumers * 32 * 12 <= (size_t)L.pairs * 2 * L.row_bytes;
+}
+
+template <int V, int NQ>
 static cudaError_t launch_v(const ScanArgs &a, int grid, cudaStream_t stream) {
-    const TmaLayout L = tma_layout(a.dim, a.k);
-    scan_tma_kernel<V><<<grid, kTmaThreads, L.total, stream>>>(a);
+    const TmaLayout L = tma_layout(a.dim, a.k, NQ);
+    scan_tma_kernel<V, NQ><<<grid, kTmaThreads, L.total, stream>>>(a);
     return cudaGetLastError();
+}
+
+template <int V>
+static cudaError_t launch_nq(const ScanArgs &a, int grid, cudaStream_t stream) {
+    switch (a.nq) {
+        case 0: case 1: return launch_v<V, 1>(a, grid, stream);
+        case 2: return launch_v<V, 2>(a, grid, stream);
+        case 4: return launch_v<V, 4>(a, grid, stream);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+template <int V>
+static cudaError_t prepare_v(int bytes) {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<V, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<V, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    return cudaFuncSetAttribute(scan_tma_kernel<V, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 // opt in to > 48 KB dynamic shared memory; call once per device with that device current
 cudaError_t scan_tma_prepare() {
     cudaError_t e;
     const int bytes = (int)kSmemBudget - 8192;  // static smem (exchange buffers, flags) takes the rest
-    if ((e = cudaFuncSetAttribute(scan_tma_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
-    if ((e = cudaFuncSetAttribute(scan_tma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
-    if ((e = cudaFuncSetAttribute(scan_tma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
-    if ((e = cudaFuncSetAttribute(scan_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
-    if ((e = cudaFuncSetAttribute(scan_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
-    return cudaSuccess;
+    if ((e = prepare_v<6>(bytes))) return e;
+    if ((e = prepare_v<8>(bytes))) return e;
+    if ((e = prepare_v<4>(bytes))) return e;
+    if ((e = prepare_v<2>(bytes))) return e;
+    return prepare_v<1>(bytes);
 }
 
 cudaError_t launch_scan_tma(const ScanArgs &a_in, int grid, cudaStream_t stream) {
@@ -360,11 +564,11 @@ cudaError_t launch_scan_tma(const ScanArgs &a_in, int grid, cudaStream_t stream)
     while (cg > 1 && ngroups / cg < (uint32_t)grid * kProducers * 4u) cg >>= 1;
     a.chunk_groups = cg;
     switch (a.dim) {
-        case 768: return launch_v<6>(a, grid, stream);
-        case 1024: return launch_v<8>(a, grid, stream);
-        case 512: return launch_v<4>(a, grid, stream);
-        case 256: return launch_v<2>(a, grid, stream);
-        case 128: return launch_v<1>(a, grid, stream);
+        case 768: return launch_nq<6>(a, grid, stream);
+        case 1024: return launch_nq<8>(a, grid, stream);
+        case 512: return launch_nq<4>(a, grid, stream);
+        case 256: return launch_nq<2>(a, grid, stream);
+        case 128: return launch_nq<1>(a, grid, stream);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -1,0 +1,84 @@
+"""Small-batch scans: 2 or 4 queries share one pass over the store (spl_scan_tma.cu, NQ > 1), so each row
+fetched from HBM is scored for all of them.  Same contract as the single-query scan; the per-row
+arithmetic is the same instruction sequence, so a batch must return bit-for-bit what the same queries
+return one at a time, and both must match the CPU oracle."""
+import numpy as np
+import pytest
+
+import libsplinter_b200 as sg
+import support
+
+pytestmark = pytest.mark.gpu
+
+
+def _mirror(n, dim, seed=1234):
+    E, bloom, flags = support.synth_dense(seed, 99, 0, n, dim)
+    m = sg.Mirror.open_dense(n, dim)
+    m.dense_upload(0, E, bloom, flags)
+    return m, E, bloom, flags
+
+
+@pytest.fixture(scope="module")
+def corpus():
+    m, E, bloom, flags = _mirror(40_003, 768)
+    yield m, E, bloom, flags, support.synth_queries(777, 8, 768)
+    m.close()
+
+
+@pytest.mark.parametrize("nq", [2, 3, 4, 5, 7, 8])
+@pytest.mark.parametrize("k", [1, 10, 32])
+def test_batch_equals_one_at_a_time_and_the_oracle(corpus, nq, k):
+    m, E, bloom, flags, q = corpus
+    out, counts = m.search(q[:nq], k, mode=sg.MODE_FAST, bloom_mask=0x1)
+    ref, rc = support.oracle_search_dense(q[:nq], E, bloom, flags, k=k, bloom_mask=0x1)
+    totals = m.last_totals(nq)
+    for i in range(nq):
+        one, c1 = m.search(q[i], k, mode=sg.MODE_FAST, bloom_mask=0x1)
+        assert counts[i] == c1[0]
+        assert out[i][:counts[i]].tobytes() == one[0][:c1[0]].tobytes()
+        support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
+        assert totals[i] == m.last_totals(1)[0]
+
+
+@pytest.mark.parametrize("order", [sg.ORDER_COSINE, sg.ORDER_L2])
+def test_thresholds_exclude_and_orders(corpus, order):
+    m, E, bloom, flags, q = corpus
+    kw = dict(order=order, bloom_mask=0x2, min_similarity=0.02, max_distance=1.41, exclude_slot=17)
+    out, counts = m.search(q[:6], 16, mode=sg.MODE_FAST, **kw)
+    ref, rc = support.oracle_search_dense(q[:6], E, bloom, flags, k=16, order=order, bloom_mask=0x2, min_sim=0.02,
+                                          max_dist=1.41, exclude=17)
+    full, fc = support.oracle_search_dense(q[:6], E, bloom, flags, k=0, order=order, bloom_mask=0x2, min_sim=0.02,
+                                           max_dist=1.41, exclude=17)
+    totals = m.last_totals(6)
+    for i in range(6):
+        support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]], order=order)
+        assert abs(int(totals[i]) - int(fc[i])) <= 2      # rows sitting within an ulp of a threshold
+
+
+def test_exact_mode_rides_the_same_batched_scan(corpus):
+    m, E, bloom, flags, q = corpus
+    out, counts = m.search(q[:5], 10, mode=sg.MODE_EXACT, bloom_mask=0x3)
+    ref, rc = support.oracle_search_dense(q[:5], E, bloom, flags, k=10, bloom_mask=0x3)
+    for i in range(5):
+        support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]], exact=True)
+
+
+@pytest.mark.parametrize("dim", [1024, 512, 128])
+def test_other_dims_and_no_candidates(dim):
+    m, E, bloom, flags = _mirror(9_001, dim, seed=5)
+    q = support.synth_queries(11, 4, dim)
+    for mask in (0, 1 << 63, (1 << 64) - 1):
+        out, counts = m.search(q, 10, mode=sg.MODE_FAST, bloom_mask=mask)
+        ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=10, bloom_mask=mask)
+        for i in range(4):
+            assert counts[i] == rc[i]
+            support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
+    m.close()
+
+
+def test_identical_queries_in_one_batch_give_identical_lists(corpus):
+    m, E, bloom, flags, q = corpus
+    qq = np.repeat(q[:1], 4, axis=0)
+    out, counts = m.search(qq, 10, mode=sg.MODE_FAST)
+    for i in range(1, 4):
+        assert counts[i] == counts[0] and out[i].tobytes() == out[0].tobytes()
