@@ -339,6 +339,29 @@ def run_ours(args):
                               "scanned_GB_per_s": round(b / ms_v / 1e6, 1), "roofline_frac": round(b / ms_v / 1e6 / peak, 4),
                               "algorithmic_bytes": b}
 
+    # ---- small batch: 4 queries per call share one pass over the store (fp32 scan kernel, NQ = 4) ----
+    small = None
+    if single:
+        small = {}
+        q4 = torch.stack([q_dev[i] for i in range(4)]).contiguous()
+        out4 = torch.zeros((4 * k, 32), dtype=torch.uint8, device=dev)
+        cnt4 = torch.zeros(4, dtype=torch.int32, device=dev)
+        for name, mask in (("mask_0x3", C2_MASK), ("mask_all_match_bit63", 1 << 63)):
+            p4 = m.params(4, k, mode=sg.MODE_FAST, bloom_mask=mask)
+            for _ in range(args.warmup):
+                m.search_device(p4, q4.data_ptr(), out4.data_ptr(), k, cnt4.data_ptr(), stream)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.steps):
+                m.search_device(p4, q4.data_ptr(), out4.data_ptr(), k, cnt4.data_ptr(), stream)
+            e1.record()
+            barrier()
+            ms4 = e0.elapsed_time(e1) / args.steps
+            b = algorithmic_bytes(total_rows, n_pass_of(mask))
+            small[name] = {"queries_per_call": 4, "ms_per_call": round(ms4, 4), "queries_per_s": round(4e3 / ms4, 1),
+                           "hbm_GB_per_s": round(b / ms4 / 1e6, 1), "speedup_vs_one_at_a_time": None}
+
     # ---- C3: batched 256-query L2 top-32 on the tensor cores (rides along at N = 1) ----
     c3 = c3_batched_leg(sg, support, torch, dev, stream, args) if single else None
 
@@ -370,6 +393,11 @@ def run_ours(args):
         }
         if variants:
             line["variants"] = variants
+        if small:
+            small["mask_0x3"]["speedup_vs_one_at_a_time"] = round(small["mask_0x3"]["queries_per_s"] * ms_step / 1e3, 3)
+            small["mask_all_match_bit63"]["speedup_vs_one_at_a_time"] = round(
+                small["mask_all_match_bit63"]["queries_per_s"] * variants["mask_all_match_bit63"]["ms_per_step"] / 1e3, 3)
+            line["small_batch_4q"] = small
         if c3:
             line["c3_batched"] = c3
         if single and not args.skip_cpu:

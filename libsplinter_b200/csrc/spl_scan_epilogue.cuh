@@ -162,69 +162,103 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
     }
 }
 
-// ---- small-batch scans: NQ queries, each with NW per-warp lists of k <= 32 entries ---------------------
-// Lists of (query qi, warp w) sit at skeys/sidx[(qi*NW + w) * k]; xk/xi is an exchange buffer of NQ*NW*32
-// entries (the idle row ring).  All NQ merges share the same barriers.  Query qi writes a.out + qi*out_stride,
-// a.out_count[qi], a.total[qi]; its survivor count was accumulated in counters[2 + qi].
-template <int NW, int NQ>
-__device__ __forceinline__ void tree_merge32_multi(uint64_t (&key)[NQ], uint32_t (&idx)[NQ], uint64_t *xk, uint32_t *xi) {
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int step = 1; step < NW; step <<= 1) {
-        if (warp < NW && (warp & (2 * step - 1)) == step) {
-#pragma unroll
-            for (int qi = 0; qi < NQ; qi++) { xk[(qi * NW + warp) * 32 + lane] = key[qi]; xi[(qi * NW + warp) * 32 + lane] = idx[qi]; }
+// ---- compact epilogue for k <= 32 (TMA scan kernel; nq = 1, 2 or 4 queries) ------------------------------
+// Same three steps as scan_epilogue_small, written as ROLLED loops around one instance of each building block.
+// The epilogue runs once per CTA, so its instructions are always cold: measured, the time of the unrolled
+// version (~30 KB of straight-line code per query) was mostly instruction fetch, about 0.45 us per KB.
+// Lists of (query qi, warp w) sit at skeys/sidx[(qi*NW + w) * k].  `scratch` (the idle row ring, at least
+// kEpilogueScratchBytes) holds the tree-merge exchange buffer and, in the last CTA, a staging area so that the
+// loads of all published lists of a round are in flight together while the merges run as a rolled loop.
+// Query qi writes a.out + qi*out_stride, a.out_count[qi*count_stride], a.total[qi] (from counters[2 + qi]).
+__device__ __forceinline__ void warp_sort32_rolled(uint64_t &key, uint32_t &idx, uint32_t lane) {
+#pragma unroll 1
+    for (uint32_t size = 2; size <= 32; size <<= 1) {
+#pragma unroll 1
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            const uint64_t ok = __shfl_xor_sync(0xffffffffu, key, stride);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, idx, stride);
+            const bool up = (lane & size) == 0, lower = (lane & stride) == 0;
+            const bool other_first = better(ok, oi, key, idx);
+            if ((lower == up) ? other_first : !other_first) { key = ok; idx = oi; }
         }
-        __syncthreads();
-        if (warp < NW && (warp & (2 * step - 1)) == 0 && warp + step < NW) {
-#pragma unroll
-            for (int qi = 0; qi < NQ; qi++)
-                warp_merge32(key[qi], idx[qi], xk[(qi * NW + warp + step) * 32 + lane], xi[(qi * NW + warp + step) * 32 + lane], lane);
-        }
-        // no second barrier: a region written at one level is never written again at a later one
     }
 }
-
-template <int NW, int NQ>
-__device__ __forceinline__ void scan_epilogue_small_multi(const ScanArgs &a, const uint64_t *skeys, const uint32_t *sidx,
-                                                          uint64_t *xk, uint32_t *xi, uint32_t *s_flag) {
-    const uint32_t k = a.k, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    __syncthreads();  // lists final, ring idle
-    uint64_t key[NQ]; uint32_t idx[NQ];
-#pragma unroll
-    for (int qi = 0; qi < NQ; qi++) {
-        key[qi] = kKeySentinel; idx[qi] = kIdxSentinel;
-        if (warp < NW && lane < k) { key[qi] = skeys[(qi * NW + warp) * k + lane]; idx[qi] = sidx[(qi * NW + warp) * k + lane]; }
-        if (warp < NW) warp_sort32(key[qi], idx[qi], lane);
+__device__ __forceinline__ void warp_merge32_rolled(uint64_t &key, uint32_t &idx, uint64_t bkey, uint32_t bidx, uint32_t lane) {
+    const uint64_t rk = __shfl_sync(0xffffffffu, bkey, 31 - lane);
+    const uint32_t ri = __shfl_sync(0xffffffffu, bidx, 31 - lane);
+    if (better(rk, ri, key, idx)) { key = rk; idx = ri; }
+#pragma unroll 1
+    for (uint32_t stride = 16; stride > 0; stride >>= 1) {
+        const uint64_t ok = __shfl_xor_sync(0xffffffffu, key, stride);
+        const uint32_t oi = __shfl_xor_sync(0xffffffffu, idx, stride);
+        const bool lower = (lane & stride) == 0;
+        const bool other_first = better(ok, oi, key, idx);
+        if (lower ? other_first : !other_first) { key = ok; idx = oi; }
     }
-    tree_merge32_multi<NW, NQ>(key, idx, xk, xi);
-    if (warp == 0 && lane < k) {
-#pragma unroll
-        for (int qi = 0; qi < NQ; qi++) {
-            Cand c; c.key = key[qi]; c.idx = idx[qi]; c.pad = 0;
+}
+template <int NW>
+__device__ __forceinline__ void cta_tree_merge32_rolled(uint64_t &key, uint32_t &idx, uint64_t *xk, uint32_t *xi) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll 1
+    for (uint32_t step = 1; step < NW; step <<= 1) {
+        if (warp < NW && (warp & (2 * step - 1)) == step) { xk[warp * 32 + lane] = key; xi[warp * 32 + lane] = idx; }
+        __syncthreads();
+        if (warp < NW && (warp & (2 * step - 1)) == 0 && warp + step < NW)
+            warp_merge32_rolled(key, idx, xk[(warp + step) * 32 + lane], xi[(warp + step) * 32 + lane], lane);
+        // no barrier here: a region written at one level is not written again at a later one
+    }
+    __syncthreads();  // the buffer is free again for the next call
+}
+
+constexpr int kFoldBatch = 10;  // published lists a warp loads per round (148 CTAs / 16 warps: one round)
+template <int NW>
+constexpr uint32_t epilogue_scratch_bytes() { return NW * 32 * 12 + NW * kFoldBatch * 32 * 12; }
+
+template <int NW>
+__device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_t nq, const uint64_t *skeys, const uint32_t *sidx,
+                                                      unsigned char *scratch, uint32_t *s_flag) {
+    const uint32_t k = a.k, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *xk = reinterpret_cast<uint64_t *>(scratch);
+    uint32_t *xi = reinterpret_cast<uint32_t *>(xk + NW * 32);
+    uint64_t *fk = reinterpret_cast<uint64_t *>(scratch + NW * 32 * 12);
+    uint32_t *fi = reinterpret_cast<uint32_t *>(fk + NW * kFoldBatch * 32);
+    __syncthreads();  // lists final, ring idle
+    // 1 + 2. per query: every warp sorts its list, tree merge, warp 0 publishes the CTA's k best
+#pragma unroll 1
+    for (uint32_t qi = 0; qi < nq; qi++) {
+        uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
+        if (warp < NW && lane < k) { key = skeys[(qi * NW + warp) * k + lane]; idx = sidx[(qi * NW + warp) * k + lane]; }
+        if (warp < NW) warp_sort32_rolled(key, idx, lane);
+        cta_tree_merge32_rolled<NW>(key, idx, xk, xi);
+        if (warp == 0 && lane < k) {
+            Cand c; c.key = key; c.idx = idx; c.pad = 0;
             a.cta_cands[((size_t)qi * gridDim.x + blockIdx.x) * k + lane] = c;
         }
     }
-    __threadfence();
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 4] = gtime_ns();
+    if (warp == 0) __threadfence();  // the only warp that published
     __syncthreads();
     if (threadIdx.x == 0) {
         const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
         *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
     }
     __syncthreads();
+    if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 5] = gtime_ns();
     if (*s_flag == 0) return;
-    // last CTA: fold every CTA's published list, query by query
+    // 3. last CTA, per query: each warp folds a strided subset of the gridDim.x published (sorted) lists
     __threadfence();
-#pragma unroll
-    for (int qi = 0; qi < NQ; qi++) {
-        key[qi] = kKeySentinel; idx[qi] = kIdxSentinel;
+#pragma unroll 1
+    for (uint32_t qi = 0; qi < nq; qi++) {
+        uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
         if (warp < NW) {
-            constexpr int kBatch = 10;
             const Cand *lists = a.cta_cands + (size_t)qi * gridDim.x * k;
-            for (uint32_t c0 = warp; c0 < gridDim.x; c0 += NW * kBatch) {
-                uint64_t bk[kBatch]; uint32_t bi[kBatch];
+            uint64_t *wk = fk + warp * kFoldBatch * 32;
+            uint32_t *wi = fi + warp * kFoldBatch * 32;
+#pragma unroll 1
+            for (uint32_t c0 = warp; c0 < gridDim.x; c0 += NW * kFoldBatch) {
+                uint64_t bk[kFoldBatch]; uint32_t bi[kFoldBatch];
 #pragma unroll
-                for (int j = 0; j < kBatch; j++) {
+                for (int j = 0; j < kFoldBatch; j++) {  // all loads of the round in flight together
                     const uint32_t c = c0 + j * NW;
                     bk[j] = kKeySentinel; bi[j] = kIdxSentinel;
                     if (c < gridDim.x && lane < k) {
@@ -234,41 +268,49 @@ __device__ __forceinline__ void scan_epilogue_small_multi(const ScanArgs &a, con
                     }
                 }
 #pragma unroll
-                for (int j = 0; j < kBatch; j++)
-                    if (c0 + j * NW < gridDim.x) warp_merge32(key[qi], idx[qi], bk[j], bi[j], lane);
+                for (int j = 0; j < kFoldBatch; j++) { wk[j * 32 + lane] = bk[j]; wi[j * 32 + lane] = bi[j]; }
+                __syncwarp();
+                const uint32_t left = (gridDim.x - c0 + NW - 1) / NW;
+                const uint32_t nl = left < (uint32_t)kFoldBatch ? left : (uint32_t)kFoldBatch;
+#pragma unroll 1
+                for (uint32_t j = 0; j < nl; j++) warp_merge32_rolled(key, idx, wk[j * 32 + lane], wi[j * 32 + lane], lane);
+                __syncwarp();
             }
         }
-    }
-    tree_merge32_multi<NW, NQ>(key, idx, xk, xi);
-    if (warp == 0) {
-#pragma unroll
-        for (int qi = 0; qi < NQ; qi++) {
-            const unsigned valid = __ballot_sync(0xffffffffu, lane < k && idx[qi] != kIdxSentinel);
+        if (a.dbg && threadIdx.x == 0 && qi == 0) a.dbg[blockIdx.x * 8 + 6] = gtime_ns();
+        cta_tree_merge32_rolled<NW>(key, idx, xk, xi);
+        if (a.dbg && threadIdx.x == 0 && qi == 0) a.dbg[blockIdx.x * 8 + 7] = gtime_ns();
+        if (warp == 0) {
+            const unsigned valid = __ballot_sync(0xffffffffu, lane < k && idx != kIdxSentinel);
             if (lane == 0) {
                 a.out_count[(size_t)qi * a.count_stride] = __popc(valid);
                 if (a.total) a.total[qi] = *reinterpret_cast<volatile uint32_t *>(&a.counters[2 + qi]);
             }
-            if (lane < k && idx[qi] != kIdxSentinel) {
+            if (lane < k && idx != kIdxSentinel) {
                 spl_gpu_result r;
-                split_key(a.order, key[qi], r.similarity, r.distance);
-                r.slot_idx = (uint32_t)(a.row0 + idx[qi]);
-                r.has_embedding = (a.flags[idx[qi]] & SPL_ROW_EMB) ? 1u : 0u;
-                r.epoch = a.epoch[idx[qi]];
-                r.bloom = a.bloom[idx[qi]];
+                split_key(a.order, key, r.similarity, r.distance);
+                r.slot_idx = (uint32_t)(a.row0 + idx);
+                r.has_embedding = (a.flags[idx] & SPL_ROW_EMB) ? 1u : 0u;
+                r.epoch = a.epoch[idx];
+                r.bloom = a.bloom[idx];
                 a.out[(size_t)qi * a.out_stride + lane] = r;
             }
         }
+    }
+    if (warp == 0) {
         __syncwarp();
-        if (lane < 2 + NQ) a.counters[lane] = 0;
+        if (lane < 2 + nq) a.counters[lane] = 0;
     }
 }
 
 // workspace the final merge may use: `ws_entries` (power of two, >= 2*k) entries at ws_keys/ws_idx
-template <int NW>
+template <int NW, bool SMALL = true>
 __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys, uint32_t *sidx, uint64_t *ws_keys,
                                               uint32_t *ws_idx, uint32_t ws_entries, uint32_t *s_flag) {
     const uint32_t k = a.k;
-    if (k <= 32) { scan_epilogue_small<NW>(a, skeys, sidx, s_flag); return; }  // registers + shuffles
+    if constexpr (SMALL) {
+        if (k <= 32) { scan_epilogue_small<NW>(a, skeys, sidx, s_flag); return; }  // registers + shuffles
+    }
     const uint32_t P = next_pow2(NW * k);  // the lists region is padded to P entries (sentinel-filled)
     __syncthreads();
     bitonic_sort_cta(skeys, sidx, P);

@@ -130,7 +130,8 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32
     const uint32_t avail = kSmemBudget - 8192u - L.rows_off;      // 8 KB headroom for static smem
     const uint32_t p = avail / (2 * L.row_bytes);
     L.pairs = p > kMaxPairs ? kMaxPairs : p;
-    L.total = L.rows_off + L.pairs * 2 * L.row_bytes;
+    const uint32_t ring = L.pairs * 2 * L.row_bytes, scratch = epilogue_scratch_bytes<kConsumers>();
+    L.total = L.rows_off + (ring > scratch ? ring : scratch);     // the idle ring doubles as the epilogue's scratch
     return L;
 }
 
@@ -502,8 +503,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
     uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
     uint64_t *ws_keys = reinterpret_cast<uint64_t *>(smem + L.rows_off);
     uint32_t *ws_idx = reinterpret_cast<uint32_t *>(ws_keys + ws_entries);
-    if constexpr (NQ == 1) scan_epilogue<kConsumers>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
-    else scan_epilogue_small_multi<kConsumers, NQ>(a, skeys, sidx, ws_keys, reinterpret_cast<uint32_t *>(ws_keys + NQ * kConsumers * 32), &s_flag);
+    if (NQ > 1 || a.k <= 32) scan_epilogue_compact<kConsumers>(a, NQ, skeys, sidx, smem + L.rows_off, &s_flag);
+    else scan_epilogue<kConsumers, false>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 3] = gtime();
 }
 
@@ -517,7 +518,7 @@ bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq) {
     if (nq != 2 && nq != 4) return false;
     if (k == 0 || k > 32 || !scan_tma_supported(dim, k)) return false;
     const TmaLayout L = tma_layout(dim, k, nq);
-    return L.pairs >= kMinPairs && (size_t)nq * kConsumers * 32 * 12 <= (size_t)L.pairs * 2 * L.row_bytes;
+    return L.pairs >= kMinPairs;
 }
 
 template <int V, int NQ>

@@ -1,5 +1,7 @@
 import json,sys
-for ln in sys.stdin:
+# usage: bench_summary.py FILE   (or pipe the bench output in)
+src = open(sys.argv[1]) if len(sys.argv) > 1 else sys.stdin
+for ln in src:
     if ln.startswith("{"):
         d=json.loads(ln)
         print("head ms", d["ms_per_step"], "GB/s", d["value"], "frac", d["roofline"]["frac"], "| e2e ms", d["e2e"]["ms_per_step"], "| parity", d["parity"].get("ok"), d["parity"].get("indices_identical"))
