@@ -101,37 +101,51 @@ def have_ref() -> bool:
     return (REF_DIR / "libref_search.so").exists() and (REF_DIR / "libsplinter.so").exists()
 
 
+def _bind_store(lib):
+    lib.splinter_create.restype = C.c_int
+    lib.splinter_create.argtypes = [C.c_char_p, C.c_size_t, C.c_size_t]
+    lib.splinter_open.restype = C.c_int
+    lib.splinter_open.argtypes = [C.c_char_p]
+    lib.splinter_close.restype = None
+    lib.splinter_set.restype = C.c_int
+    lib.splinter_set.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t]
+    lib.splinter_unset.restype = C.c_int
+    lib.splinter_unset.argtypes = [C.c_char_p]
+    lib.splinter_set_embedding.restype = C.c_int
+    lib.splinter_set_embedding.argtypes = [C.c_char_p, _vp]
+    lib.splinter_get_embedding.restype = C.c_int
+    lib.splinter_get_embedding.argtypes = [C.c_char_p, _vp]
+    lib.splinter_set_label.restype = C.c_int
+    lib.splinter_set_label.argtypes = [C.c_char_p, _u64]
+    lib.splinter_unset_label.restype = C.c_int
+    lib.splinter_unset_label.argtypes = [C.c_char_p, _u64]
+    lib.splinter_retrain_slot.restype = C.c_int
+    lib.splinter_retrain_slot.argtypes = [C.c_char_p]
+    lib.splinter_bump_slot.restype = C.c_int
+    lib.splinter_bump_slot.argtypes = [C.c_char_p]
+    lib.splinter_enumerate_matches.restype = None
+    lib.splinter_list.restype = C.c_int
+    lib.splinter_event_bus_init.restype = C.c_int
+    return lib
+
+
 def ref_store() -> C.CDLL:
     """The reference's own libsplinter.so (compiled unmodified by oracle/Makefile)."""
     global _ref_store
     if _ref_store is None:
-        lib = C.CDLL(str(REF_DIR / "libsplinter.so"), mode=C.RTLD_GLOBAL)
-        lib.splinter_create.restype = C.c_int
-        lib.splinter_create.argtypes = [C.c_char_p, C.c_size_t, C.c_size_t]
-        lib.splinter_open.restype = C.c_int
-        lib.splinter_open.argtypes = [C.c_char_p]
-        lib.splinter_close.restype = None
-        lib.splinter_set.restype = C.c_int
-        lib.splinter_set.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t]
-        lib.splinter_unset.restype = C.c_int
-        lib.splinter_unset.argtypes = [C.c_char_p]
-        lib.splinter_set_embedding.restype = C.c_int
-        lib.splinter_set_embedding.argtypes = [C.c_char_p, _vp]
-        lib.splinter_get_embedding.restype = C.c_int
-        lib.splinter_get_embedding.argtypes = [C.c_char_p, _vp]
-        lib.splinter_set_label.restype = C.c_int
-        lib.splinter_set_label.argtypes = [C.c_char_p, _u64]
-        lib.splinter_unset_label.restype = C.c_int
-        lib.splinter_unset_label.argtypes = [C.c_char_p, _u64]
-        lib.splinter_retrain_slot.restype = C.c_int
-        lib.splinter_retrain_slot.argtypes = [C.c_char_p]
-        lib.splinter_bump_slot.restype = C.c_int
-        lib.splinter_bump_slot.argtypes = [C.c_char_p]
-        lib.splinter_enumerate_matches.restype = None
-        lib.splinter_list.restype = C.c_int
-        lib.splinter_event_bus_init.restype = C.c_int
-        _ref_store = lib
+        _ref_store = _bind_store(C.CDLL(str(REF_DIR / "libsplinter.so"), mode=C.RTLD_GLOBAL))
     return _ref_store
+
+
+_ref_store_p = None
+
+
+def ref_store_persistent() -> C.CDLL:
+    """The same source built with -DSPLINTER_PERSISTENT: file-backed stores (splinter.c:157-168, 237-241)."""
+    global _ref_store_p
+    if _ref_store_p is None:
+        _ref_store_p = _bind_store(C.CDLL(str(REF_DIR / "libsplinter_p.so"), mode=C.RTLD_LOCAL))
+    return _ref_store_p
 
 
 def ref_search() -> C.CDLL:
