@@ -427,23 +427,46 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
     const uint32_t R = next_pow2(m < 2 ? 2 : m);
     for (uint32_t i = threadIdx.x; i < R; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = kIdxSentinel; }
     __syncthreads();
-    // |q|^2 (fp32) once per warp
-    const float *qv = q32 + (size_t)q * a.dim;
+    // Exact fp32 re-score of the m best.  Each row is 4*dim bytes somewhere in HBM: the loop is written so that a
+    // warp has two whole rows (2 x dim/128 independent 16-byte loads per lane) in flight at a time -- with scalar
+    // loads in a rolled loop this step was latency-bound and took longer than everything else in the kernel.
+    // Same per-lane arithmetic order for every row, so equal rows get equal scores.
+    const float4 *qv4 = reinterpret_cast<const float4 *>(q32 + (size_t)q * a.dim);
+    const uint32_t nv = a.dim >> 2;  // float4s per row; dim is a multiple of 64 on this path
     float ma = 0.f;
-    for (uint32_t d = lane; d < a.dim; d += 32) ma = fmaf(qv[d], qv[d], ma);
+    for (uint32_t d = lane; d < nv; d += 32) {
+        const float4 y = qv4[d];
+        ma = fmaf(y.x, y.x, ma); ma = fmaf(y.y, y.y, ma); ma = fmaf(y.z, y.z, ma); ma = fmaf(y.w, y.w, ma);
+    }
     ma = warp_sum(ma);
-    for (uint32_t c = warp; c < m; c += blockDim.x / 32) {
-        const uint32_t row = idx[c];
-        const float *e = a.E + (size_t)row * a.dim;
-        float dot = 0.f, mb = 0.f, ss = 0.f;
-        for (uint32_t d = lane; d < a.dim; d += 32) {
-            const float x = e[d], y = qv[d], t = y - x;
-            dot = fmaf(y, x, dot); mb = fmaf(x, x, mb); ss = fmaf(t, t, ss);
+    auto score_row = [&](const float4 *e4, float &dot, float &mb, float &ss) {
+        dot = 0.f; mb = 0.f; ss = 0.f;
+#pragma unroll 8
+        for (uint32_t d = lane; d < nv; d += 32) {
+            const float4 x = __ldg(e4 + d), y = qv4[d];
+            float t;
+            dot = fmaf(y.x, x.x, dot); mb = fmaf(x.x, x.x, mb); t = y.x - x.x; ss = fmaf(t, t, ss);
+            dot = fmaf(y.y, x.y, dot); mb = fmaf(x.y, x.y, mb); t = y.y - x.y; ss = fmaf(t, t, ss);
+            dot = fmaf(y.z, x.z, dot); mb = fmaf(x.z, x.z, mb); t = y.z - x.z; ss = fmaf(t, t, ss);
+            dot = fmaf(y.w, x.w, dot); mb = fmaf(x.w, x.w, mb); t = y.w - x.w; ss = fmaf(t, t, ss);
         }
+    };
+    auto emit = [&](uint32_t c, uint32_t row, float dot, float mb, float ss) {
         dot = warp_sum(dot); mb = warp_sum(mb); ss = warp_sum(ss);
         float sim = cosine_from_sums(dot, ma, mb), dist = __fsqrt_rn(ss);
         if (!(a.flags[row] & SPL_ROW_EMB)) { sim = 0.f; dist = FLT_MAX; }
         if (lane == 0) { rk[c] = make_key(a.order, sim, dist); ri[c] = row; }
+    };
+    const uint32_t nwarps = blockDim.x / 32;
+    for (uint32_t c = warp; c < m; c += 2 * nwarps) {
+        const uint32_t c2 = c + nwarps;
+        const bool two = c2 < m;
+        const uint32_t row0 = idx[c], row1 = two ? idx[c2] : row0;
+        float d0, b0, s0, d1, b1, s1;
+        score_row(reinterpret_cast<const float4 *>(a.E + (size_t)row0 * a.dim), d0, b0, s0);
+        score_row(reinterpret_cast<const float4 *>(a.E + (size_t)row1 * a.dim), d1, b1, s1);
+        emit(c, row0, d0, b0, s0);
+        if (two) emit(c2, row1, d1, b1, s1);
     }
     __syncthreads();
     bitonic_sort_cta(rk, ri, R);
