@@ -303,7 +303,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 float tmin = INFINITY;
                 uint32_t imin = kIdxSentinel;
 #pragma unroll 1
-                for (uint32_t c0 = 0; c0 < (a.pass == 3 ? 0u : (uint32_t)BN); c0 += 32) {  // pass 3: developer probe, no epilogue math
+                for (uint32_t c0 = 0; c0 < (uint32_t)BN; c0 += 32) {
                     uint32_t v[32];
                     tc_ld32(tmem_base + ((quad * 32u) << 16) + acc * BN + c0, v);
                     const float4 *pa4 = reinterpret_cast<const float4 *>(pa + c0), *pb4 = reinterpret_cast<const float4 *>(pb + c0);
@@ -613,7 +613,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
                                                        a.thr_row);
     if ((e = cudaGetLastError())) return e;
     // pass 2: every tile, append what beats the threshold
-    a.pass = getenv("SPL_GPU_BATCH_PROBE") ? 3 : 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
+    a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     static bool attr = false;
     const size_t sel_smem = (size_t)kBatchCandCap * 12;

@@ -1113,28 +1113,13 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             const uint32_t nq = (p->nq - q0 < c->q_cap) ? p->nq - q0 : c->q_cap;
             spl_gpu_search_params pp = *p;
             pp.nq = nq;
-            static const bool probe = getenv("SPL_GPU_DEBUG_E2E") != nullptr;
-            static double acc[4]; static int calls;
-            auto T0 = std::chrono::steady_clock::now();
             memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
             CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
-            auto T1 = std::chrono::steady_clock::now();
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
             memset(c->h_total + q0, 0, nq * sizeof(uint32_t));  // mapped memory; ordered before the launch below
             if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream, c->m_total + q0))) return rc;
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
-            auto T2 = std::chrono::steady_clock::now();
             CUDA_TRY(cudaStreamSynchronize(c->stream));
-            auto T3 = std::chrono::steady_clock::now();
-            if (probe) {
-                acc[0] += std::chrono::duration<double, std::micro>(T1 - T0).count();
-                acc[1] += std::chrono::duration<double, std::micro>(T2 - T1).count();
-                acc[2] += std::chrono::duration<double, std::micro>(T3 - T2).count();
-                if (++calls % 200 == 0) {
-                    fprintf(stderr, "[e2e probe] memcpy call %.1f us, launch call %.1f us, sync wait %.1f us\n", acc[0] / 200, acc[1] / 200, acc[2] / 200);
-                    acc[0] = acc[1] = acc[2] = 0;
-                }
-            }
             if (c->timing) {
                 float ms = 0.f;
                 CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
