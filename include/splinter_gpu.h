@@ -48,11 +48,13 @@ typedef struct spl_gpu_ctx spl_gpu_ctx;
 #define SPL_ORDER_L2     1u /* distance asc, similarity desc, idx asc (batched L2 config) */
 
 /* ---- compute mode ------------------------------------------------------------------ */
-#define SPL_MODE_AUTO    0u /* FAST; from 16 queries up BATCH_BF16 when a bf16 mirror exists and no threshold is set */
+#define SPL_MODE_AUTO    0u /* FAST (2-15 queries share passes 4 or 2 at a time); from 16 queries up BATCH_BF16 when a bf16
+                               mirror exists and no threshold is set on the score that does not order the result */
 #define SPL_MODE_FAST    1u /* fp32, per-lane partial sums + warp-shuffle tree (|d sim| ~1e-6)           */
 #define SPL_MODE_EXACT   2u /* fp32, the reference's sequential summation order: scores and order bit-identical
                                to the reference (fast candidate scan + sequential re-score with a selection proof) */
-#define SPL_MODE_BATCH_BF16 3u /* tcgen05 Q x E^T on the bf16 mirror, fp32 accumulate, fp32 re-rank     */
+#define SPL_MODE_BATCH_BF16 3u /* tcgen05 Q x E^T on the bf16 mirror, fp32 accumulate, fp32 re-rank; thresholds only on
+                                  the ordering score (cosine: min_similarity, L2: max_distance), else ENOSYS */
 
 /* ---- attach options ---------------------------------------------------------------- */
 #define SPL_OPT_PERSISTENT   0x1u /* name is a file path (open), not a shm name (shm_open): splinter.c:237-241 */

@@ -470,7 +470,22 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
     }
     __syncthreads();
     bitonic_sort_cta(rk, ri, R);
-    const uint32_t nout = m < k ? m : k;
+    // threshold on the ordering score (_search.c:398-399): the rows that fail are the tail of the sorted list
+    __shared__ uint32_t s_nout;
+    if (threadIdx.x == 0) s_nout = m < k ? m : k;
+    __syncthreads();
+    if (a.min_sim > 0.f || a.max_dist > 0.f) {
+        const uint32_t lim = s_nout;
+        __syncthreads();
+        for (uint32_t t = threadIdx.x; t < lim; t += blockDim.x) {
+            float sim, dist;
+            split_key(a.order, rk[t], sim, dist);
+            const bool emb = (a.flags[ri[t]] & SPL_ROW_EMB) != 0;   // no embedding + any threshold: dropped (_search.c:392-393)
+            if (!emb || (a.min_sim > 0.f && sim < a.min_sim) || (a.max_dist > 0.f && dist > a.max_dist)) atomicMin(&s_nout, t);
+        }
+        __syncthreads();
+    }
+    const uint32_t nout = s_nout;
     for (uint32_t t = threadIdx.x; t < nout; t += blockDim.x) {
         spl_gpu_result r;
         split_key(a.order, rk[t], r.similarity, r.distance);

@@ -23,6 +23,8 @@ struct BatchArgs {
     uint64_t mask;
     uint32_t exclude;             // local row or kIdxSentinel
     uint64_t row0;
+    float min_sim, max_dist;      // threshold on the ORDERING score only (cosine: min_sim, L2: max_dist); 0 = none.
+                                  // Rows failing it are the tail of the sorted result, so it is applied after the re-score.
     // schedule
     uint32_t pass;                // 1: per-tile minima, 2: append below threshold
     uint32_t tile_first, tile_stride, n_tiles;

@@ -894,17 +894,23 @@ static int ensure_batch_scratch(spl_gpu_ctx *c, uint32_t k) {
     return 0;
 }
 
+// The batched path re-scores a fixed number of candidates chosen by the ordering score, so it can honour a
+// threshold on THAT score (the failing rows are the tail of the result) but not one on the other score.
+static bool batch_thresholds_ok(const spl_gpu_search_params *p) {
+    return p->order == SPL_ORDER_COSINE ? !(p->max_distance > 0.f) : !(p->min_similarity > 0.f);
+}
+
 static bool wants_batch(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {
     if (p->mode == SPL_MODE_BATCH_BF16) return true;
-    return p->mode == SPL_MODE_AUTO && p->nq >= 16 && c->m.E16 && batch_supported(c->dim, p->k) &&
-           !(p->min_similarity > 0.f) && !(p->max_distance > 0.f);
+    return p->mode == SPL_MODE_AUTO && p->nq >= 16 && c->m.E16 && batch_supported(c->dim, p->k) && batch_thresholds_ok(p);
 }
 
 static int check_batch(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {
     if (!c->m.E16) return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available: attach with SPL_OPT_BF16_MIRROR");
     if (!batch_supported(c->dim, p->k)) return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available for dim %u / k %u (dim %% 64 == 0, 1 <= k <= 128)", c->dim, p->k);
-    if (p->min_similarity > 0.f || p->max_distance > 0.f)
-        return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available with --similarity / --distance thresholds");
+    if (!batch_thresholds_ok(p))
+        return fail(-1, ENOSYS, "SPL_MODE_BATCH_BF16 is not available with a threshold on the score that does not order the result "
+                                "(cosine order takes --similarity, L2 order takes --distance)");
     return 0;
 }
 
@@ -915,6 +921,7 @@ static int enqueue_batch(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
     memset(&b, 0, sizeof b);
     b.E = c->m.E; b.E16 = c->m.E16; b.norm2 = c->m.norm2; b.bloom = c->m.bloom; b.flags = c->m.flags; b.epoch = c->m.epoch;
     b.n = (uint32_t)c->n; b.dim = c->dim; b.nq = nq; b.order = p->order; b.mask = p->bloom_mask;
+    b.min_sim = p->min_similarity; b.max_dist = p->max_distance;
     b.exclude = kIdxSentinel;
     if (p->exclude_slot != SPL_NO_SLOT && p->exclude_slot >= c->slot_begin && p->exclude_slot < c->slot_begin + c->n)
         b.exclude = (uint32_t)(p->exclude_slot - c->slot_begin);

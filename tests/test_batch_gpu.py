@@ -21,7 +21,8 @@ def _mirror(n, dim, row0=0, seed=1234):
 def _check(m, E, bloom, flags, q, k, row0=0, **kw):
     out, counts = m.search(q, k, mode=sg.MODE_BATCH_BF16, **kw)
     ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=k, order=kw.get("order", sg.ORDER_COSINE),
-                                          bloom_mask=kw.get("bloom_mask", 0))
+                                          bloom_mask=kw.get("bloom_mask", 0), min_sim=kw.get("min_similarity", 0.0),
+                                          max_dist=kw.get("max_distance", 0.0))
     bad = 0
     for i in range(q.shape[0]):
         got = out[i][:counts[i]].copy()
@@ -89,3 +90,38 @@ def test_batched_mode_needs_the_bf16_mirror():
     with sg.Mirror.open_dense(1000, 1024) as m:
         with pytest.raises(sg.SplinterGpuError, match="not available"):
             m.search(np.zeros((4, 1024), np.float32), 10, mode=sg.MODE_BATCH_BF16)
+
+
+def test_batched_threshold_on_the_ordering_score():
+    """--similarity with cosine order / --distance with L2 order cut the tail of the sorted result, so the
+    batched path can honour them; a threshold on the other score needs every row's exact value and is refused."""
+    n, dim = 40_000, 768
+    m, E, bloom, flags = _mirror(n, dim)
+    # the synthetic corpus' zero vectors all sit at distance |q| = 1 from every unit query: with them in play an L2
+    # threshold would fall on hundreds of exact ties.  Take them out of the candidate set for this test.
+    flags = flags.copy()
+    flags[~E.any(axis=1)] = 0
+    m.dense_upload(0, E, bloom, flags)
+    q = support.synth_queries(99, 24, dim)
+    try:
+        # thresholds chosen so that some queries keep all k, some only a few, some none
+        full, _ = support.oracle_search_dense(q, E, bloom, flags, k=16)
+        cut = float(np.median(full[:, 7]["similarity"]))
+        _check(m, E, bloom, flags, q, 16, order=sg.ORDER_COSINE, min_similarity=cut)
+        fl2, _ = support.oracle_search_dense(q, E, bloom, flags, k=16, order=sg.ORDER_L2)
+        cut_d = float(np.median(fl2[:, 7]["distance"]))
+        _check(m, E, bloom, flags, q, 16, order=sg.ORDER_L2, max_distance=cut_d)
+        _check(m, E, bloom, flags, q, 16, order=sg.ORDER_L2, max_distance=cut_d, bloom_mask=0x1)
+        with pytest.raises(sg.SplinterGpuError, match="not available"):
+            m.search(q, 16, mode=sg.MODE_BATCH_BF16, order=sg.ORDER_COSINE, max_distance=1.0)
+        with pytest.raises(sg.SplinterGpuError, match="not available"):
+            m.search(q, 16, mode=sg.MODE_BATCH_BF16, order=sg.ORDER_L2, min_similarity=0.1)
+        # AUTO with the cross threshold quietly takes the fp32 scan instead
+        out, counts = m.search(q, 16, order=sg.ORDER_COSINE, max_distance=cut_d)
+        ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=16, max_dist=cut_d)
+        for i in range(q.shape[0]):
+            assert abs(int(counts[i]) - int(rc[i])) <= 1      # a row within an ulp of the threshold
+            n_cmp = min(counts[i], rc[i])
+            support.assert_topk_matches(out[i][:n_cmp], ref[i][:n_cmp])
+    finally:
+        m.close()
