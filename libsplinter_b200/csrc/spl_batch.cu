@@ -328,7 +328,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
 #pragma unroll
                         for (int i = 0; i < 32; i++) {
                             const float t = __uint_as_float(v[i]);
-                            if (t <= thr && (t < thr || row0 + c0 + i <= thr_row)) {
+                            // t = +inf marks a row that is not a candidate (or lies past the shard's end); it must stay out
+                            // even when the bound itself is +inf (fewer sampled tiles than k')
+                            if (t < INFINITY && t <= thr && (t < thr || row0 + c0 + i <= thr_row)) {
                                 const uint32_t pos = atomicAdd(&a.cand_cnt[q], 1u);
                                 if (pos < a.cand_cap) {
                                     a.cand_t[(size_t)q * a.cand_cap + pos] = t;

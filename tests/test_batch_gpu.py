@@ -125,3 +125,22 @@ def test_batched_threshold_on_the_ordering_score():
             support.assert_topk_matches(out[i][:n_cmp], ref[i][:n_cmp])
     finally:
         m.close()
+
+
+def test_fewer_candidates_than_k():
+    """Found by tests/test_fuzz_gpu.py: with fewer sampled tiles than k' the bound is +inf, and rows marked
+    "not a candidate" (t = +inf, including the padding past the shard's end) used to tie with it and leak into
+    the candidate list.  About a quarter of the 257 rows carry the mask here and k = 128: exactly those rows must come back."""
+    n, dim = 257, 768
+    m, E, bloom, flags = _mirror(n, dim)
+    q = support.synth_queries(5, 20, dim)
+    try:
+        for order in (sg.ORDER_L2, sg.ORDER_COSINE):
+            out, counts = m.search(q, 128, mode=sg.MODE_BATCH_BF16, order=order, bloom_mask=0x3)
+            ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=128, order=order, bloom_mask=0x3)
+            assert rc[0] < 128
+            for i in range(20):
+                assert counts[i] == rc[i]
+                assert set(out[i][:counts[i]]["slot_idx"].tolist()) == set(ref[i][:rc[i]]["idx"].tolist())
+    finally:
+        m.close()
