@@ -112,6 +112,11 @@ struct TmaLayout {
     uint32_t pairs, row_bytes, rows_off, full_off, empty_off, meta_off, clist_off, state_off, q_off, list_entries, total;
 };
 
+// Which consumer loop a launch uses.  Small batches keep the queries in shared memory by construction; so does a
+// single 1024-d query: with the query in registers as well (32 + 64 row registers of the 96 available) that
+// instantiation spilled and ran a dense scan at 79 % of the bandwidth the shared-memory variant reaches.
+__host__ __device__ constexpr bool tma_query_in_smem(uint32_t dim, uint32_t nq) { return nq > 1 || dim >= 1024; }
+
 // nq > 1 (small-batch scan): nq * kConsumers lists of k entries, their bookkeeping words and the nq
 // queries themselves live in shared memory as well; the ring gets what is left.
 __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32_t nq = 1) {
@@ -124,9 +129,10 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32
     L.meta_off = L.empty_off + kMaxPairs * 8;                     // uint4 {row0, flags0, row1, flags1}
     L.clist_off = L.meta_off + kMaxPairs * 16;                    // per producer warp: 256 x {row, flags}
     L.state_off = L.clist_off + kProducers * 256 * 8;             // nq > 1: uint4 per (query, consumer warp)
-    L.q_off = L.state_off + (nq > 1 ? nq * kConsumers * 20u + 16u : 0u);  // + u32 survivors per list, |q|^2 per query
-                                                                  // nq > 1: the queries, fp32 [nq][dim], go here
-    L.rows_off = (L.q_off + (nq > 1 ? nq * L.row_bytes : 0u) + 127u) & ~127u;
+    const bool qs = tma_query_in_smem(dim, nq);
+    L.q_off = L.state_off + (qs ? nq * kConsumers * 20u + 16u : 0u);  // + u32 survivors per list, |q|^2 per query
+                                                                  // then the queries, fp32 [nq][dim]
+    L.rows_off = (L.q_off + (qs ? nq * L.row_bytes : 0u) + 127u) & ~127u;
     const uint32_t avail = kSmemBudget - 8192u - L.rows_off;      // 8 KB headroom for static smem
     const uint32_t p = avail / (2 * L.row_bytes);
     L.pairs = p > kMaxPairs ? kMaxPairs : p;
@@ -156,7 +162,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     topk_lists_init(skeys, sidx, list_entries);
-    if constexpr (NQ > 1) {
+    constexpr bool QS = tma_query_in_smem(V * 128, NQ);
+    if constexpr (QS) {
         uint4 *wstate = reinterpret_cast<uint4 *>(smem + L.state_off);
         for (uint32_t i = threadIdx.x; i < NQ * kConsumers; i += blockDim.x) {
             wstate[i] = make_uint4((uint32_t)kKeySentinel, (uint32_t)(kKeySentinel >> 32), kIdxSentinel, 0u);
@@ -294,7 +301,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                 mbar_arrive(full0 + 8 * slot);
             }
         }
-    } else if constexpr (NQ == 1) {
+    } else if constexpr (!QS) {
         // ================================ consumers ================================
         const float4 *q4 = reinterpret_cast<const float4 *>(a.q);
         float4 qv[V];
