@@ -181,3 +181,30 @@ def test_rings_whose_slots_rotate_between_consumer_warps(mode, dim, k):
             out, counts = m.search(q, k, mode=mode)
             for i in range(q.shape[0]):
                 support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]], exact=(mode == sg.MODE_EXACT))
+
+
+@pytest.mark.parametrize("k", [10, 32])
+def test_best_rows_clustered_in_one_chunk(k):
+    """The last CTA first tries a selection bounded by the k-th best list head; when every good row sits in one
+    CTA's range that bound is loose, more candidates survive than the fast path takes, and the general merge
+    fold must give the same answer.  Also a batch of four (each query with its own cluster)."""
+    n, dim = 60_000, 768
+    E, bloom, flags = support.synth_dense(77, 99, 0, n, dim)
+    q = support.synth_queries(78, 4, dim)
+    rng = np.random.default_rng(79)
+    for qi in range(4):      # 100 consecutive rows close to query qi: one 256-row chunk holds the whole top-k
+        base = 5_000 + 10_000 * qi
+        noise = rng.standard_normal((100, dim)).astype(np.float32) * np.float32(0.02)
+        E[base:base + 100] = q[qi][None, :] + noise
+        flags[base:base + 100] = sg.ROW_LIST | sg.ROW_ENUM | sg.ROW_EMB
+    m = sg.Mirror.open_dense(n, dim)
+    try:
+        m.dense_upload(0, E, bloom, flags)
+        for mode in MODES:
+            out, counts = _check(m, E, bloom, flags, q, k, mode)
+            for qi in range(4):
+                base = 5_000 + 10_000 * qi
+                assert np.all((out[qi][:k]["slot_idx"] >= base) & (out[qi][:k]["slot_idx"] < base + 100))
+            _check(m, E, bloom, flags, q[:1], k, mode, order=sg.ORDER_L2)
+    finally:
+        m.close()
