@@ -374,7 +374,8 @@ def run_ours(args):
         traffic = None
         tp = ROOT / "profiles" / "roofline_traffic.json"
         if tp.exists():
-            traffic = json.loads(tp.read_text()).get("c2_mask3_dram_bytes_per_launch" if single else "c4_dram_bytes_per_launch")
+            tj = json.loads(tp.read_text())
+            traffic = tj.get("c2_mask3_dram_bytes_per_launch") if single else tj.get("c4_dram_bytes_per_launch_by_gpus", {}).get(str(world))
         line = {
             "metric": "scanned_GB_per_s", "value": round(gbs, 2), "unit": "GB/s",
             "queries_per_s": round(1e3 / ms_step, 2),
