@@ -42,6 +42,7 @@ constexpr int kStages = 4, kAcc = 2;
 constexpr int kThreadsGemm = 256;
 constexpr uint32_t kStageA = BM * BK * 2, kStageB = BN * BK * 2, kStageBytes = kStageA + kStageB;
 constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kMaxSampledTiles = 16384;  // pass-1 sample size cap (a power of two): 192 KB of sort space per query
 
 // ---- smem carve-up (dynamic, 1024-byte aligned for SWIZZLE_128B) ----
 struct GemmSmem {
@@ -537,7 +538,12 @@ static bool make_map(CUtensorMap *map, const void *base, uint64_t rows, uint32_t
 cudaError_t batch_prepare() {
     cudaError_t e = cudaFuncSetAttribute(gemm_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmem::total);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmemPair::total);
+    e = cudaFuncSetAttribute(gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmemPair::total);
+    if (e != cudaSuccess) return e;
+    // function attributes are per device: set here (once per context, its device current), not lazily behind a flag
+    e = cudaFuncSetAttribute(select_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBatchCandCap * 12));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kMaxSampledTiles * 12));
 }
 
 static cudaError_t launch_gemm(const CUtensorMap &mapQ, const CUtensorMap &mapE, const BatchArgs &a, bool pair, int grid,
@@ -623,6 +629,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     uint32_t sampled = tiles / (frac ? frac : 1);
     if (sampled < 4 * kprime) sampled = 4 * kprime;
     if (sampled > tiles) sampled = tiles;
+    if (sampled > kMaxSampledTiles) sampled = kMaxSampledTiles;   // threshold_kernel sorts the sample in shared memory
     a.pass = 1; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = sampled;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
@@ -632,12 +639,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     // pass 2: every tile, append what beats the threshold
     a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
-    static bool attr = false;
-    const size_t sel_smem = (size_t)kBatchCandCap * 12;
-    if (!attr) {
-        if ((e = cudaFuncSetAttribute(select_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem))) return e;
-        attr = true;
-    }
+    const size_t sel_smem = (size_t)kBatchCandCap * 12;   // opted in by batch_prepare()
     select_rerank_kernel<<<a.nq, 256, sel_smem, s>>>(a, d_q32, k, kprime, d_out, out_stride, d_counts, overflow);
     if ((e = cudaGetLastError())) return e;
     *launches = 5;

@@ -171,6 +171,7 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     CUDA_TRY(cudaEventCreate(&c->ev1));
     CUDA_TRY(scan_tma_prepare());
     CUDA_TRY(batch_prepare());
+    CUDA_TRY(merge_prepare());
     const char *impl = getenv("SPL_GPU_SCAN_IMPL");  // developer knob: "ldg" forces the register-path kernel
     c->force_ldg = impl && strcmp(impl, "ldg") == 0;
     const char *multi = getenv("SPL_GPU_SCAN_MULTI");

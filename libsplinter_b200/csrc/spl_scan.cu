@@ -306,19 +306,17 @@ merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32
     else if (threadIdx.x == 0 && slot[0] == kIdxSentinel) *out_count = 0;
 }
 
+// opt in to > 48 KB dynamic shared memory; function attributes are per device: call once per context
+cudaError_t merge_prepare() {
+    return cudaFuncSetAttribute(merge_results_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kMergeMaxEntries * 16));
+}
+
 cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,
                                  uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out,
                                  uint32_t *out_count, cudaStream_t stream) {
     const uint32_t entries = topk_pow2(nlists * stride > k ? nlists * stride : k + 1);
     if (entries > kMergeMaxEntries) return cudaErrorInvalidValue;
     const size_t smem = (size_t)entries * 16;
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(merge_results_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)(kMergeMaxEntries * 16));
-        if (e != cudaSuccess) return e;
-        attr = true;
-    }
     const int threads = entries >= 2048 ? 1024 : (entries >= 512 ? 256 : 128);
     merge_results_kernel<<<1, threads, smem, stream>>>(lists, counts, nlists, stride, order, k, entries, out, out_count);
     return cudaGetLastError();

@@ -65,6 +65,7 @@ bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq);
 cudaError_t scan_tma_prepare();
 cudaError_t launch_scan_tma(const ScanArgs &a, int grid, cudaStream_t stream);
 
+cudaError_t merge_prepare();
 // merge nlists lists of Cand-like results (spl_gpu_result records) into the top-k
 cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,
                                  uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out,
