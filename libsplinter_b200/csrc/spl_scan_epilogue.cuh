@@ -441,13 +441,66 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
     __syncthreads();
     if (*s_flag == 0) return;
 
-    // ---- last CTA: running top-k over gridDim.x * k published candidates, a workspace-full at a time ----
+    // ---- last CTA ----
     __threadfence();
-    const uint32_t total = gridDim.x * k;
+    const uint32_t G = gridDim.x, total = G * k;
+    // Bounded selection first (cf. scan_epilogue_compact).  Every published list is sorted; take its entry at
+    // position p as an ANCHOR and let T be the s-th best anchor, s = ceil(k / (p+1)): s lists hold p+1 entries at
+    // least as good as T each, i.e. at least k candidates are <= T, so nothing worse than T can be among the k
+    // best.  With the best rows spread over the CTAs only a few hundred of the G*k candidates survive, and ONE
+    // sort of them replaces sorting all G*k (a 2^20-row top-100 spent 240 us there, three times the scan itself).
+    bool done = false;
+    {
+        __shared__ uint32_t s_cnt2, s_ti2;
+        __shared__ uint64_t s_tk2;
+        const uint32_t p = k / 100, s = (k + p) / (p + 1);   // p = 0 up to k = 99, 1 up to 199, 2 up to 256
+        if (G <= ws_entries && s <= G) {   // (uniform)
+            if (threadIdx.x == 0) { s_cnt2 = 0; s_tk2 = kKeySentinel; s_ti2 = kIdxSentinel; }
+            for (uint32_t c = threadIdx.x; c < G; c += blockDim.x) {
+                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + (size_t)c * k + p));
+                ws_keys[c] = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
+                ws_idx[c] = (uint32_t)raw.z;
+            }
+            __syncthreads();
+            for (uint32_t c = threadIdx.x; c < G; c += blockDim.x) {   // rank of my anchor; ranks are distinct
+                const uint64_t mk = ws_keys[c]; const uint32_t mi = ws_idx[c];
+                if (mi == kIdxSentinel) continue;
+                uint32_t rank = 0;
+#pragma unroll 4
+                for (uint32_t j = 0; j < G; j++) rank += better(ws_keys[j], ws_idx[j], mk, mi) ? 1u : 0u;
+                if (rank == s - 1) { s_tk2 = mk; s_ti2 = mi; }   // fewer than s anchors: T stays +inf
+            }
+            __syncthreads();   // anchors are dead from here on: the workspace now collects the survivors
+            const uint64_t tk = s_tk2; const uint32_t ti = s_ti2;
+#pragma unroll 4
+            for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) {
+                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + i));
+                const uint64_t ek = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
+                const uint32_t ei = (uint32_t)raw.z;
+                if (ei != kIdxSentinel && !better(tk, ti, ek, ei)) {   // e <= T
+                    const uint32_t pos = atomicAdd(&s_cnt2, 1u);
+                    if (pos < ws_entries) { ws_keys[pos] = ek; ws_idx[pos] = ei; }
+                }
+            }
+            __syncthreads();
+            const uint32_t cnt = s_cnt2;
+            if (cnt <= ws_entries) {
+                uint32_t lo = cnt > k ? cnt : k;
+                const uint32_t W2 = next_pow2(lo < 2 ? 2 : lo);
+                for (uint32_t q = cnt + threadIdx.x; q < W2; q += blockDim.x) { ws_keys[q] = kKeySentinel; ws_idx[q] = kIdxSentinel; }
+                __syncthreads();
+                bitonic_sort_cta(ws_keys, ws_idx, W2);
+                done = true;
+            }
+            __syncthreads();
+        }
+    }
+    // general path: running top-k over the G * k published candidates, a workspace-full at a time
     const uint32_t need = next_pow2(total + k);
     const uint32_t W = need < ws_entries ? need : ws_entries;  // workspace actually sorted
-    for (uint32_t p = threadIdx.x; p < k; p += blockDim.x) { ws_keys[p] = kKeySentinel; ws_idx[p] = kIdxSentinel; }
-    for (uint32_t base = 0; base < total; base += W - k) {
+    if (!done)
+        for (uint32_t p = threadIdx.x; p < k; p += blockDim.x) { ws_keys[p] = kKeySentinel; ws_idx[p] = kIdxSentinel; }
+    for (uint32_t base = done ? total : 0u; base < total; base += W - k) {
         for (uint32_t p = k + threadIdx.x; p < W; p += blockDim.x) {
             const uint32_t src = base + (p - k);
             uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
