@@ -1,0 +1,99 @@
+"""The device-pointer entry points (spl_gpu_search_device, spl_gpu_merge_topk_device) used by the multi-GPU path:
+same results, byte for byte, as the host-buffer call on the same mirror, and shard lists that merge to the
+single-store answer.  Device buffers and the stream come from torch (plumbing only)."""
+import numpy as np
+import pytest
+
+import libsplinter_b200 as sg
+import support
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def _dev_search(m, q, k, stream, **kw):
+    nq = q.shape[0]
+    dq = torch.from_numpy(q).cuda()
+    out = torch.zeros((nq, k, 32), dtype=torch.uint8, device="cuda")
+    cnt = torch.zeros(nq, dtype=torch.int32, device="cuda")
+    p = m.params(nq, k, **kw)
+    with torch.cuda.stream(stream):
+        m.search_device(p, dq.data_ptr(), out.data_ptr(), k, cnt.data_ptr(), stream.cuda_stream)
+    stream.synchronize()
+    return out.cpu().numpy().view(sg.RESULT_DTYPE).reshape(nq, k), cnt.cpu().numpy().astype(np.uint32), out, cnt
+
+
+@pytest.mark.parametrize("mode", [sg.MODE_FAST, sg.MODE_EXACT, sg.MODE_AUTO])
+@pytest.mark.parametrize("nq,k", [(1, 10), (5, 10), (4, 32), (3, 100)])
+def test_device_buffers_give_the_host_call_s_bytes(mode, nq, k):
+    n, dim = 30_000, 768
+    E, bloom, flags = support.synth_dense(1234, 99, 0, n, dim)
+    q = support.synth_queries(55, nq, dim)
+    stream = torch.cuda.Stream()
+    with sg.Mirror.open_dense(n, dim) as m:
+        m.dense_upload(0, E, bloom, flags)
+        for kw in (dict(bloom_mask=0x1), dict(order=sg.ORDER_L2, bloom_mask=0x2, exclude_slot=11)):
+            host, hc = m.search(q, k, mode=mode, **kw)
+            dev, dc, _, _ = _dev_search(m, q, k, stream, mode=mode, **kw)
+            assert np.array_equal(hc, dc)
+            for i in range(nq):
+                assert host[i][:hc[i]].tobytes() == dev[i][:dc[i]].tobytes()
+
+
+def test_shard_lists_merge_to_the_single_store_answer():
+    n, dim, k, shards = 45_000, 768, 20, 3
+    E, bloom, flags = support.synth_dense(77, 99, 0, n, dim)
+    q = support.synth_queries(56, 1, dim)
+    stream = torch.cuda.Stream()
+    with sg.Mirror.open_dense(n, dim) as whole:
+        whole.dense_upload(0, E, bloom, flags)
+        want, wc = whole.search(q, k, bloom_mask=0x1)
+    per = n // shards
+    lists, counts, mirrors = [], [], []
+    try:
+        for s in range(shards):
+            lo, hi = s * per, (n if s == shards - 1 else (s + 1) * per)
+            m = sg.Mirror.open_dense(hi - lo, dim, global_row0=lo)
+            m.dense_upload(0, E[lo:hi], bloom[lo:hi], flags[lo:hi])
+            mirrors.append(m)
+            _, _, d_out, d_cnt = _dev_search(m, q, k, stream, bloom_mask=0x1)
+            lists.append(d_out.reshape(k, 32)); counts.append(d_cnt)
+        gathered = torch.cat(lists).contiguous()          # what all_gather_into_tensor delivers on every rank
+        gcnt = torch.cat(counts).contiguous()
+        fin = torch.zeros((k, 32), dtype=torch.uint8, device="cuda")
+        fcnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+        with torch.cuda.stream(stream):
+            mirrors[0].merge_topk_device(gathered.data_ptr(), gcnt.data_ptr(), shards, k, sg.ORDER_COSINE, k,
+                                         fin.data_ptr(), fcnt.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        got = fin.cpu().numpy().view(sg.RESULT_DTYPE).reshape(k)
+        assert int(fcnt.item()) == int(wc[0]) == k
+        assert got.tobytes() == want[0][:k].tobytes()     # global slot indices, same order, same scores
+        # ragged: one shard contributes nothing, another only a few
+        gcnt2 = gcnt.clone(); gcnt2[1] = 0; gcnt2[2] = 3
+        with torch.cuda.stream(stream):
+            mirrors[0].merge_topk_device(gathered.data_ptr(), gcnt2.data_ptr(), shards, k, sg.ORDER_COSINE, k,
+                                         fin.data_ptr(), fcnt.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        got = fin.cpu().numpy().view(sg.RESULT_DTYPE).reshape(k)[:int(fcnt.item())]
+        pool = np.concatenate([lists[0].cpu().numpy().view(sg.RESULT_DTYPE).reshape(k)[:int(gcnt[0])],
+                               lists[2].cpu().numpy().view(sg.RESULT_DTYPE).reshape(k)[:3]])
+        order = np.lexsort((pool["slot_idx"], pool["distance"], -pool["similarity"]))
+        assert got.tobytes() == pool[order][:k].tobytes()
+    finally:
+        for m in mirrors:
+            m.close()
+
+
+def test_batched_mode_through_device_buffers():
+    n, dim, nq, k = 20_000, 1024, 40, 16
+    E, bloom, flags = support.synth_dense(5, 99, 0, n, dim)
+    q = support.synth_queries(57, nq, dim)
+    stream = torch.cuda.Stream()
+    with sg.Mirror.open_dense(n, dim, flags=sg.OPT_BF16_MIRROR) as m:
+        m.dense_upload(0, E, bloom, flags)
+        host, hc = m.search(q, k, mode=sg.MODE_BATCH_BF16, order=sg.ORDER_L2)
+        dev, dc, _, _ = _dev_search(m, q, k, stream, mode=sg.MODE_BATCH_BF16, order=sg.ORDER_L2)
+        assert np.array_equal(hc, dc)
+        for i in range(nq):
+            assert host[i][:hc[i]].tobytes() == dev[i][:dc[i]].tobytes()
