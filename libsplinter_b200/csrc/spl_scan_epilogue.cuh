@@ -277,7 +277,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     __shared__ uint32_t s_cnt, s_tidx;
     __shared__ uint64_t s_tkey;
     const uint32_t G = gridDim.x;
-    const bool one_round = G <= (uint32_t)(NW * kFoldBatch);
+    const bool one_round = G <= 160u && G * k <= 8u * blockDim.x;   // the fast path's register budget (below)
     uint64_t *hk = xk, *sk = xk + 256;        // heads / survivors live in the (idle) tree-merge exchange buffer
     uint32_t *hi = xi, *si = xi + 256;
 #pragma unroll 1
@@ -286,28 +286,29 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
         const Cand *lists = a.cta_cands + (size_t)qi * G * k;
         bool done = false;
         if (one_round) {
-            if (warp < NW) {   // stage every list: list c sits at slot (c % NW) * kFoldBatch + c / NW, 32 entries each
-                uint64_t *wk = fk + warp * kFoldBatch * 32;
-                uint32_t *wi = fi + warp * kFoldBatch * 32;
-                uint64_t bk[kFoldBatch]; uint32_t bi[kFoldBatch];
-#pragma unroll
-                for (int j = 0; j < kFoldBatch; j++) {  // all loads in flight together
-                    const uint32_t c = warp + j * NW;
-                    bk[j] = kKeySentinel; bi[j] = kIdxSentinel;
-                    if (c < G && lane < k) {
-                        const int4 raw = __ldcg(reinterpret_cast<const int4 *>(lists + (size_t)c * k + lane));
-                        bk[j] = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
-                        bi[j] = (uint32_t)raw.z;
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < kFoldBatch; j++) { wk[j * 32 + lane] = bk[j]; wi[j * 32 + lane] = bi[j]; }
-            }
+            // every candidate is loaded once, straight into registers (all loads of a thread in flight together);
+            // a list's first entry doubles as its head
+            constexpr int kPerThread = 8;
+            uint64_t ck[kPerThread]; uint32_t ci[kPerThread];
+            const uint32_t total = G * k;   // <= 160 * 32 = 5120 <= kPerThread * 640
             if (threadIdx.x == 0) { s_cnt = 0; s_tkey = kKeySentinel; s_tidx = kIdxSentinel; }
-            __syncthreads();
-            if (threadIdx.x < G) {
-                const uint32_t slot = ((threadIdx.x % NW) * kFoldBatch + threadIdx.x / NW) * 32;
-                hk[threadIdx.x] = fk[slot]; hi[threadIdx.x] = fi[slot];
+#pragma unroll
+            for (int j = 0; j < kPerThread; j++) {
+                const uint32_t i = threadIdx.x + j * blockDim.x;
+                ck[j] = kKeySentinel; ci[j] = kIdxSentinel;
+                if (i < total) {
+                    const int4 raw = __ldcg(reinterpret_cast<const int4 *>(lists + i));
+                    ck[j] = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
+                    ci[j] = (uint32_t)raw.z;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kPerThread; j++) {
+                const uint32_t i = threadIdx.x + j * blockDim.x;
+                if (i < total) {
+                    const uint32_t c = i / k;
+                    if (i == c * k) { hk[c] = ck[j]; hi[c] = ci[j]; }
+                }
             }
             __syncthreads();
             {   // rank of every head among all heads (the order is total, so ranks are distinct): four threads per
@@ -330,14 +331,11 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
             }
             __syncthreads();
             const uint64_t tk = s_tkey; const uint32_t ti = s_tidx;
-            if (lane < k) {
-                for (uint32_t c = warp; c < G; c += blockDim.x >> 5) {
-                    const uint32_t slot = ((c % NW) * kFoldBatch + c / NW) * 32 + lane;
-                    const uint64_t ek = fk[slot]; const uint32_t ei = fi[slot];
-                    if (ei != kIdxSentinel && !better(tk, ti, ek, ei)) {   // e <= T
-                        const uint32_t pos = atomicAdd(&s_cnt, 1u);
-                        if (pos < 64) { sk[pos] = ek; si[pos] = ei; }
-                    }
+#pragma unroll
+            for (int j = 0; j < kPerThread; j++) {
+                if (ci[j] != kIdxSentinel && !better(tk, ti, ck[j], ci[j])) {   // e <= T
+                    const uint32_t pos = atomicAdd(&s_cnt, 1u);
+                    if (pos < 64) { sk[pos] = ck[j]; si[pos] = ci[j]; }
                 }
             }
             __syncthreads();
