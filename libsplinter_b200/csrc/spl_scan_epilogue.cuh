@@ -336,6 +336,11 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
                 if (ci[j] != kIdxSentinel && !better(tk, ti, ck[j], ci[j])) {   // e <= T
                     const uint32_t pos = atomicAdd(&s_cnt, 1u);
                     if (pos < 64) { sk[pos] = ck[j]; si[pos] = ci[j]; }
+                    // the record of a winner needs three more words of its row; the scan has pushed them out of
+                    // L2 long ago, so start fetching while the sort runs
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.flags + ci[j]));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.epoch + ci[j]));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.bloom + ci[j]));
                 }
             }
             __syncthreads();
