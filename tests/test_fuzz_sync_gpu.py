@@ -65,3 +65,46 @@ def test_random_mutations_then_sync(seed, dim):
                 ref, _ = support.oracle_search_image(img, q[i], 10, bloom_mask=mask)
                 support.assert_topk_matches(out[0][:cnt[0]], ref)
         assert m.sync().rows_uploaded == 0       # quiescent: nothing to do
+
+
+def test_batched_search_follows_incremental_sync():
+    """Config C5's combination: dirty-slot re-upload into BOTH mirrors (fp32 rows and the tiled bf16 shadow with
+    its norms) and the tensor-core path searching them.  After every sync the batched result must equal the oracle
+    on the store image."""
+    rng = np.random.default_rng(12)
+    dim, slots, nkeys = 256, 2048, 1500
+    img = support.new_image(slots, 64, dim)
+    keys = [f"k{i:05d}" for i in range(nkeys)]
+
+    def unit():
+        v = rng.standard_normal(dim).astype(np.float32)
+        return v / np.linalg.norm(v)
+
+    for key in keys[:1200]:
+        support.image_set(img, key, b"v")
+        support.image_set_embedding(img, key, unit())
+        if rng.integers(0, 2):
+            support.image_set_label(img, key, 0x1)
+    q = np.stack([unit() for _ in range(20)])
+    with sg.Mirror.attach_image(img, flags=sg.OPT_BF16_MIRROR, sync_threads=3) as m:
+        assert m.info().has_bf16_mirror == 1
+        for rnd in range(12):
+            for _ in range(int(rng.integers(20, 200))):
+                key = keys[int(rng.integers(0, nkeys))]
+                op = int(rng.integers(0, 6))
+                if op <= 2:
+                    support.image_set(img, key, b"v")
+                    support.image_set_embedding(img, key, unit())
+                elif op == 3:
+                    support.image_set_label(img, key, 0x1)
+                elif op == 4:
+                    support.image_unset_label(img, key, 0x1)
+                else:
+                    support.image_unset(img, key)
+            m.sync()
+            for order, mask in ((sg.ORDER_COSINE, 0), (sg.ORDER_L2, 0x1)):
+                out, cnt = m.search(q, 8, mode=sg.MODE_BATCH_BF16, order=order, bloom_mask=mask)
+                for i in range(q.shape[0]):
+                    ref, _ = support.oracle_search_image(img, q[i], 8, order=order, bloom_mask=mask)
+                    assert cnt[i] == len(ref)
+                    support.assert_topk_matches(out[i][:cnt[i]], ref, order=order)
