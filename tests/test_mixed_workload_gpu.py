@@ -46,7 +46,7 @@ def test_concurrent_writers_sync_and_search():
         vec[2:] = np.float32(1.0) + np.arange(2, DIM, dtype=np.float32) / np.float32(1024.0)
         assert ref.splinter_set_embedding(key, support._p(vec)) == 0
     try:
-        m = sg.Mirror.attach(name, sync_threads=4)
+        m = sg.Mirror.attach(name, sync_threads=4, flags=sg.OPT_BF16_MIRROR)   # syncs also maintain the bf16 shadow
         writer = str(support.REF_DIR / "ref_writer")
         procs = [subprocess.Popen([writer, name, str(lo), str(lo + NKEYS // 4), str(1000 + lo), "2500"],
                                   stdout=subprocess.PIPE, text=True) for lo in range(0, NKEYS, NKEYS // 4)]
@@ -55,10 +55,14 @@ def test_concurrent_writers_sync_and_search():
 
         def searcher():  # searches run concurrently with syncs from another thread
             q = np.ones((1, DIM), np.float32)
+            qb = np.random.default_rng(3).standard_normal((20, DIM)).astype(np.float32)
             while not stop.is_set():
                 out, cnt = m.search(q, 10, bloom_mask=0)
                 assert cnt[0] == 10
-                stats["searches"] += 1
+                # the batched tensor-core path reads the bf16 shadow while scatter kernels rewrite it
+                out, cnt = m.search(qb, 10, mode=sg.MODE_BATCH_BF16)
+                assert np.all(cnt == 10)
+                stats["searches"] += 2
 
         th = threading.Thread(target=searcher)
         th.start()
