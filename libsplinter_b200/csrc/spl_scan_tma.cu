@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
 #pragma unroll
             for (int j = 0; j < V; j++) x[j] = r0[32 * j];
 #pragma unroll
-            for (int j = 0; j < V; j++) y[j] = two ? r1[32 * j] : x[j];
+            for (int j = 0; j < V; j++) y[j] = r1[32 * j];   // a lone row's partner slot holds stale bytes: scored, never used
             __syncwarp();
             if (lane == 0) publish_gen(empty0 + 8 * slot, gen + 1);  // both rows now live in registers
             slot += kConsumers;
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
 #pragma unroll
             for (int j = 0; j < V; j++) x[j] = r0[32 * j];
 #pragma unroll
-            for (int j = 0; j < V; j++) y[j] = two ? r1[32 * j] : x[j];
+            for (int j = 0; j < V; j++) y[j] = r1[32 * j];   // a lone row's partner slot holds stale bytes: scored, never used
             __syncwarp();
             if (lane == 0) publish_gen(empty0 + 8 * slot, gen + 1);
             slot += kConsumers;
