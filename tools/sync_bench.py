@@ -1,7 +1,7 @@
 """Boundary-layer measurement ("upload/sync time reported separately"): full first sync of a
 2^20-slot reference-format store, idle re-sync, and incremental syncs while writer processes mutate the
 store through the reference API; searches run in between.  Run on the GPU box."""
-import json, mmap, os, subprocess, sys, time
+import json, mmap, os, subprocess, sys, threading, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np, libsplinter_b200 as sg, support
@@ -26,7 +26,7 @@ try:
     warm = sg.Mirror.open_dense(256, dim)      # CUDA context creation is not the sync layer's cost
     warm.close()
     t0 = time.perf_counter()
-    m = sg.Mirror.attach(name, sync_threads=16)
+    m = sg.Mirror.attach(name, sync_threads=16, flags=sg.OPT_BF16_MIRROR)   # C5 searches are batched: keep the bf16 shadow too
     t_attach = time.perf_counter() - t0
     st = m.sync()
     out["first_sync"] = {"attach_plus_full_sync_s": round(t_attach, 3), "rows": int(placed),
@@ -58,12 +58,26 @@ try:
         procs = [subprocess.Popen([writer, name, str(i * (nkeys // lanes)), str((i + 1) * (nkeys // lanes)), str(77 + i), "4000"],
                                   stdout=subprocess.PIPE, text=True) for i in range(lanes)]
         syncs = []
+        qb = support.synth_queries(777, 64, dim)
+        stop = threading.Event()
+        batched = dict(calls=0, secs=0.0)
+
+        def searcher():   # C5: nq = 64 batched cosine top-10 searches while the writers and the syncs run
+            while not stop.is_set():
+                t0 = time.perf_counter()
+                out, cnt = m.search(qb, 10, mode=sg.MODE_BATCH_BF16)
+                batched["secs"] += time.perf_counter() - t0
+                batched["calls"] += 1
+
+        th = threading.Thread(target=searcher)
+        th.start()
         while any(p.poll() is None for p in procs):
             t0 = time.perf_counter()
             s = m.sync()
             dt = time.perf_counter() - t0
             syncs.append((dt, s.rows_uploaded, s.meta_updated, s.skipped_busy, s.aba_rechecked, s.sweep_ms, s.upload_ms))
-            m.search(q[len(syncs) % 4], 10, bloom_mask=3)
+        stop.set()
+        th.join()
         ops = sum(int(p.communicate()[0].split()[0]) for p in procs)
         s = m.sync()
         dts = np.array([x[0] for x in syncs]); rows = np.array([x[1] for x in syncs])
@@ -73,7 +87,11 @@ try:
                                 "sweep_ms_median": round(float(np.median([x[5] for x in syncs])), 2),
                                 "upload_ms_median": round(float(np.median([x[6] for x in syncs])), 2),
                                 "dirty_rows_per_s": round(float(rows.sum() / dts.sum())),
-                                "skipped_busy_total": int(sum(x[3] for x in syncs)), "aba_rechecked_total": int(sum(x[4] for x in syncs))}
+                                "skipped_busy_total": int(sum(x[3] for x in syncs)), "aba_rechecked_total": int(sum(x[4] for x in syncs)),
+                                "writer_mix": "80% set_embedding, 10% retrain_slot, 5% set/unset_label, 5% unset+set (ref_writer default)",
+                                "batched_search": {"nq": 64, "k": 10, "mode": "BATCH_BF16 cosine", "calls": batched["calls"],
+                                                   "ms_per_call": round(batched["secs"] / max(batched["calls"], 1) * 1e3, 3),
+                                                   "queries_per_s": round(64 * batched["calls"] / max(batched["secs"], 1e-9))}}
         # quiesced: mirror == store on a sample of slots
         E, bloom, flags, epoch = m.read_mirror(0, 65536)
         Es = np.zeros((65536, dim), np.float32)
