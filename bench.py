@@ -330,6 +330,20 @@ def run_ours(args):
     clocks = clk.summary()
     ms_e2e = timed_e2e(head_mask, args.steps, args.warmup)
 
+    # per-query latency distribution (median + p99): one event between consecutive launches
+    latency = None
+    if single:
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        barrier()
+        evs[0].record()
+        for i in range(args.steps):
+            device_step(i, head_mask)
+            evs[i + 1].record()
+        barrier()
+        per = np.array([evs[i].elapsed_time(evs[i + 1]) * 1e3 for i in range(args.steps)])
+        latency = {"median": round(float(np.median(per)), 2), "p99": round(float(np.percentile(per, 99)), 2),
+                   "max": round(float(per.max()), 2), "n": int(args.steps)}
+
     variants = {}
     if single:
         for name, mask in (("mask_all_match_bit63", 1 << 63), ("unfiltered_mask_0", 0)):
@@ -392,6 +406,8 @@ def run_ours(args):
                          "kernel": "spl::scan_*_kernel (one launch per query per GPU)"},
             "parity": parity,
         }
+        if latency:
+            line["latency_us"] = latency
         if variants:
             line["variants"] = variants
         if small:
