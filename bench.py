@@ -161,7 +161,9 @@ def workload_config(n_gpus):
     return {"workload": f"C4: 2^26 slots x 768-d fp32 sharded by slot range over {n_gpus} GPUs, single-query cosine "
                         "top-100, per-GPU top-k all-gathered over NCCL + device merge",
             "slots": C4_ROWS, "dim": DIM, "k": C4_K, "bloom_mask": "0", "parallelism": f"slot-range shards x{n_gpus}",
-            "l2_policy": "inputs larger than L2"}
+            "l2_policy": "inputs larger than L2",
+            "note": "the total (2^26 slots, 206 GB) is fixed for N = 2, 4, 8 (strong scaling among them); it does not fit one "
+                    "GPU, so N = 1 runs C2 (2^20 slots) -- compare GB/s per GPU, not queries/s, across that step"}
 
 
 # ------------------------------------------------------------------------------------------ our arm
