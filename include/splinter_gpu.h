@@ -48,8 +48,9 @@ typedef struct spl_gpu_ctx spl_gpu_ctx;
 #define SPL_ORDER_L2     1u /* distance asc, similarity desc, idx asc (batched L2 config) */
 
 /* ---- compute mode ------------------------------------------------------------------ */
-#define SPL_MODE_AUTO    0u /* FAST (2-15 queries share passes 4 or 2 at a time); from 16 queries up BATCH_BF16 when a bf16
-                               mirror exists and no threshold is set on the score that does not order the result */
+#define SPL_MODE_AUTO    0u /* FAST (small batches share passes 4 or 2 queries at a time); BATCH_BF16 from 16 queries up
+                               (from 4 when no label mask is given) if a bf16 mirror exists and no threshold is set on
+                               the score that does not order the result */
 #define SPL_MODE_FAST    1u /* fp32, per-lane partial sums + warp-shuffle tree (|d sim| ~1e-6)           */
 #define SPL_MODE_EXACT   2u /* fp32, the reference's sequential summation order: scores and order bit-identical
                                to the reference (fast candidate scan + sequential re-score with a selection proof) */

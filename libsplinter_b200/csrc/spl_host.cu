@@ -903,7 +903,11 @@ static bool batch_thresholds_ok(const spl_gpu_search_params *p) {
 
 static bool wants_batch(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {
     if (p->mode == SPL_MODE_BATCH_BF16) return true;
-    return p->mode == SPL_MODE_AUTO && p->nq >= 16 && c->m.E16 && batch_supported(c->dim, p->k) && batch_thresholds_ok(p);
+    // The batched pass streams the whole bf16 shadow whatever the mask (~0.35 ms per 2^20 x 1024 rows, up to 128
+    // queries); the fp32 scan reads only the rows that pass.  Unfiltered, four queries already cost the scan twice
+    // that; with a label mask of unknown selectivity the scan keeps the small batches.
+    const uint32_t from = p->bloom_mask == 0 ? 4u : 16u;
+    return p->mode == SPL_MODE_AUTO && p->nq >= from && c->m.E16 && batch_supported(c->dim, p->k) && batch_thresholds_ok(p);
 }
 
 static int check_batch(const spl_gpu_ctx *c, const spl_gpu_search_params *p) {

@@ -59,6 +59,16 @@ def test_batched_small_shapes_and_auto_mode():
         ref, rc = support.oracle_search_dense(q16, E, bloom, flags, k=10)
         for i in range(20):
             support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
+        # which path AUTO takes, seen through the launch counter (batched = 5 launches per call, scan = one per
+        # group of up to 4 queries): unfiltered batches go to the tensor cores from 4 queries, masked ones from 16
+        def launches(nq, **kw):
+            before = m.launch_count()
+            m.search(q16[:nq], 10, **kw)
+            return m.launch_count() - before
+        assert launches(4) == 5 and launches(3) == 2                     # 3 queries: a 2-query and a 1-query scan
+        assert launches(4, bloom_mask=0x1) == 1 and launches(15, bloom_mask=0x1) == 5   # 4+4+4+2+1
+        assert launches(16, bloom_mask=0x1) == 5
+        assert launches(20, max_distance=1.0) == 5                       # cosine order + distance threshold: 5 scans of 4
     finally:
         m.close()
 
