@@ -1,20 +1,22 @@
-// spl_scan_tma.cu -- single-query fused scan, TMA-staged (the default SPL_MODE_FAST kernel).
+// spl_scan_tma.cu -- fused scan, TMA-staged (the default SPL_MODE_FAST kernel): one query, or 2 / 4 queries per pass.
 //
 // Same contract as spl_scan.cu (predicate -> cosine + L2 -> thresholds -> top-k; reference:
 // /root/reference/splinter_cli_cmd_search.c:336-416) but the embedding rows travel HBM -> shared
 // memory through the bulk-copy engine (cp.async.bulk, SASS UBLKCP) instead of through registers:
 //
-//   producer warp    evaluates the label / validity predicate for 32 slots at a time from 9 bytes
-//                    per slot (bloom u64 + flags u8) and, only for the slots that pass, issues bulk
-//                    copies of the rows into a shared-memory ring of PAIR slots (2 rows each; two
-//                    passing rows that are neighbours in HBM travel as one 8*dim-byte copy).  Rows
-//                    that fail the predicate never leave HBM.
-//   16 consumer warps each take every 16th pair slot: wait on the slot's mbarrier, pull both rows
-//                    into registers with conflict-free 128-bit LDS, hand the slot back, then score
-//                    the two rows interleaved (dot, |e|^2, sum (q-e)^2, warp-shuffle tree) and feed
-//                    the per-warp top-k list.
+//   4 producer warps  evaluate the label / validity predicate for a chunk of up to 256 slots from 9 bytes
+//                     per slot (bloom u64 + flags u8), compact the slots that pass and issue bulk copies of
+//                     their rows into a shared-memory ring of PAIR slots (2 rows each; two passing rows that
+//                     are neighbours in HBM travel as one 8*dim-byte copy).  Rows that fail the predicate
+//                     never leave HBM.
+//   16 consumer warps each take every 16th pair slot: wait on the slot's mbarrier, pull both rows into
+//                     registers with conflict-free 128-bit LDS, hand the slot back, then score the two rows
+//                     (dot, |e|^2, sum (q-e)^2 with packed FFMA2, warp-shuffle tree) and feed the per-warp
+//                     top-k list.  NQ = 1: the query sits in registers (in shared memory for 1024-d rows).
+//                     NQ = 2 / 4: the queries sit in shared memory, every row is scored against each of them,
+//                     the partial sums are reduced transposed and each (query, row) is finished by its own lane.
 //
-// One persistent CTA per SM keeps up to 192 KB of row data in flight per SM no matter what the
+// One persistent CTA per SM keeps up to ~190 KB of row data in flight per SM no matter what the
 // compute warps are doing -- what an HBM-bound gather of 3 KB rows needs.
 #include <float.h>
 
