@@ -7,7 +7,8 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np, libsplinter_b200 as sg, support
 
 slots = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 20
-nkeys = int(slots * 0.98)
+fill = float(sys.argv[2]) if len(sys.argv) > 2 else 0.98     # load factor of the reference's open-addressing table
+nkeys = int(slots * fill)
 dim, maxval = 768, 64
 name = f"/splb200_syncbench_{os.getpid()}"
 path = "/dev/shm" + name
@@ -21,7 +22,7 @@ t0 = time.perf_counter()
 assert support.oracle().splo_image_init(support._p(img), slots, maxval, dim) == 0
 placed = support.image_fill_synthetic(img, nkeys)
 t_build = time.perf_counter() - t0
-out = {"slots": slots, "keys_placed": int(placed), "store_bytes": size, "host_build_s": round(t_build, 2)}
+out = {"slots": slots, "fill": fill, "keys_placed": int(placed), "store_bytes": size, "host_build_s": round(t_build, 2)}
 try:
     warm = sg.Mirror.open_dense(256, dim)      # CUDA context creation is not the sync layer's cost
     warm.close()
@@ -71,11 +72,15 @@ try:
 
         th = threading.Thread(target=searcher)
         th.start()
+        period = float(os.environ.get("SYNC_PERIOD_MS", "0")) / 1e3    # 0 = sweep back to back
         while any(p.poll() is None for p in procs):
+            m.wait(100)                      # event bus / H->epoch gate (returns at once while writers are active)
             t0 = time.perf_counter()
             s = m.sync()
             dt = time.perf_counter() - t0
             syncs.append((dt, s.rows_uploaded, s.meta_updated, s.skipped_busy, s.aba_rechecked, s.sweep_ms, s.upload_ms))
+            if period > dt:
+                time.sleep(period - dt)      # a sweep reads one to three cache lines of EVERY slot: pace it on big stores
         stop.set()
         th.join()
         ops = sum(int(p.communicate()[0].split()[0]) for p in procs)
@@ -88,7 +93,7 @@ try:
                                 "upload_ms_median": round(float(np.median([x[6] for x in syncs])), 2),
                                 "dirty_rows_per_s": round(float(rows.sum() / dts.sum())),
                                 "skipped_busy_total": int(sum(x[3] for x in syncs)), "aba_rechecked_total": int(sum(x[4] for x in syncs)),
-                                "writer_mix": "80% set_embedding, 10% retrain_slot, 5% set/unset_label, 5% unset+set (ref_writer default)",
+                                "sync_period_ms": period * 1e3, "writer_mix": "80% set_embedding, 10% retrain_slot, 5% set/unset_label, 5% unset+set (ref_writer default)",
                                 "batched_search": {"nq": 64, "k": 10, "mode": "BATCH_BF16 cosine", "calls": batched["calls"],
                                                    "ms_per_call": round(batched["secs"] / max(batched["calls"], 1) * 1e3, 3),
                                                    "queries_per_s": round(64 * batched["calls"] / max(batched["secs"], 1e-9))}}
@@ -97,6 +102,8 @@ try:
         Es = np.zeros((65536, dim), np.float32)
         slot_size = 128 + 4 * dim
         for i in range(0, 65536, 997):
+            if not (flags[i] & 3):
+                continue          # not a live slot (never used, or unset): its mirror row is not a candidate and is left alone
             off = 5440 + i * slot_size + 128
             assert np.array_equal(E[i].view(np.uint32), img[off:off + 4 * dim].view(np.uint32)), i
         out["mirror_equals_store_after_quiesce"] = True
