@@ -500,6 +500,13 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, std::atomic<uint64_t> *nex
     const uint64_t hi = lo + chunk < c->n ? lo + chunk : c->n;
     for (uint64_t r = lo; r < hi; r++) {
         const uint8_t *sl = c->base + kHeaderSize + (c->slot_begin + r) * c->slot_size;
+        // slots are 128 + 4*dim bytes apart, so every slot's metadata is its own cache line (and, on a big store, its
+        // own TLB entry): the hardware prefetcher does not follow the stride, ask for the lines a few slots ahead
+        if (r + 12 < hi) {
+            __builtin_prefetch(sl + 12 * c->slot_size, 0, 0);
+            __builtin_prefetch(sl + 12 * c->slot_size + S_KEY, 0, 0);
+            if (header_moved) __builtin_prefetch(sl + 12 * c->slot_size + S_EMBED, 0, 0);   // the fingerprint's line
+        }
         const uint64_t h = ld_acq64(sl + S_HASH);
         const uint64_t e1 = ld_acq64(sl + S_EPOCH);
         const uint8_t st = c->c_state[r];

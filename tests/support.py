@@ -235,7 +235,14 @@ def image_slots(img):
     return int(img[8:12].view(np.uint32)[0])
 
 
+def _register(img):
+    """The oracle maps an image's base address to its dimension; a buffer it did not create itself (a file read
+    back, a copy) may sit where an earlier image of another dimension lived.  Re-derive it from the geometry."""
+    oracle().splo_image_dim(_p(img), img.nbytes)
+
+
 def image_to_dense(img, dim=768):
+    _register(img)
     n = image_slots(img)
     E = np.empty((n, dim), np.float32)
     bloom = np.empty(n, np.uint64)
@@ -264,6 +271,7 @@ def oracle_search_dense(q, E, bloom, flags, k, order=ORDER_COSINE, bloom_mask=0,
 
 def oracle_search_image(img, q, k, order=ORDER_COSINE, bloom_mask=0, min_sim=0.0, max_dist=0.0, exclude_key=None):
     q = np.ascontiguousarray(q, np.float32)
+    _register(img)
     n = image_slots(img)
     out = np.zeros(n, SPLO_RESULT)
     surv = C.c_long(0)

@@ -23,6 +23,9 @@ def _vec(rng):
 
 def _check(m, path, q, **kw):
     img = np.fromfile(path, dtype=np.uint8)     # page cache == the MAP_SHARED mapping
+    # the oracle keeps a base-address -> dimension registry for images it did not create itself; a fresh buffer
+    # can land on the address of an earlier test's image of another dimension
+    assert support.oracle().splo_image_dim(support._p(img), img.nbytes) == DIM
     okw = dict(kw)
     for mode in (sg.MODE_FAST, sg.MODE_EXACT):
         out, cnt = m.search(q, 10, mode=mode, **kw)
