@@ -170,9 +170,10 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
 // kEpilogueScratchBytes) holds the tree-merge exchange buffer and, in the last CTA, a staging area so that the
 // loads of all published lists of a round are in flight together while the merges run as a rolled loop.
 // Query qi writes a.out + qi*out_stride, a.out_count[qi*count_stride], a.total[qi] (from counters[2 + qi]).
-__device__ __forceinline__ void warp_sort32_rolled(uint64_t &key, uint32_t &idx, uint32_t lane) {
+// `width` (a power of two): only lanes [0, width) hold entries, the rest hold sentinels and need no sorting
+__device__ __forceinline__ void warp_sort32_rolled(uint64_t &key, uint32_t &idx, uint32_t lane, uint32_t width = 32) {
 #pragma unroll 1
-    for (uint32_t size = 2; size <= 32; size <<= 1) {
+    for (uint32_t size = 2; size <= width; size <<= 1) {
 #pragma unroll 1
         for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
             const uint64_t ok = __shfl_xor_sync(0xffffffffu, key, stride);
@@ -247,7 +248,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     for (uint32_t qi = 0; qi < nq; qi++) {
         uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
         if (warp < NW && lane < k) { key = skeys[(qi * NW + warp) * k + lane]; idx = sidx[(qi * NW + warp) * k + lane]; }
-        if (warp < NW) warp_sort32_rolled(key, idx, lane);
+        if (warp < NW) warp_sort32_rolled(key, idx, lane, next_pow2(k < 2 ? 2 : k));
         cta_tree_merge32_rolled<NW>(key, idx, xk, xi);
         if (warp == 0 && lane < k) {
             Cand c; c.key = key; c.idx = idx; c.pad = 0;
@@ -255,11 +256,13 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
         }
     }
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 4] = gtime_ns();
-    if (warp == 0) __threadfence();  // the only warp that published
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
-        *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
+    if (warp == 0) {   // the only warp that published: its fence, then its ticket -- no block-wide barrier needed before
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
+            *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
+        }
     }
     __syncthreads();
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 5] = gtime_ns();
