@@ -282,7 +282,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     const uint32_t G = gridDim.x;
     const bool one_round = G <= 160u && G * k <= 8u * blockDim.x;   // the fast path's register budget (below)
     uint64_t *hk = xk, *sk = xk + 256;        // heads / survivors live in the (idle) tree-merge exchange buffer
-    uint32_t *hi = xi, *si = xi + 256;
+    uint32_t *hi = xi, *si = xi + 256, *hh = xi + 320;   // hh: the heads' high words, 160 entries (16-byte aligned)
 #pragma unroll 1
     for (uint32_t qi = 0; qi < nq; qi++) {
         uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
@@ -310,25 +310,39 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
                 const uint32_t i = threadIdx.x + j * blockDim.x;
                 if (i < total) {
                     const uint32_t c = i / k;
-                    if (i == c * k) { hk[c] = ck[j]; hi[c] = ci[j]; }
+                    if (i == c * k) { hk[c] = ck[j]; hi[c] = ci[j]; hh[c] = (uint32_t)(ck[j] >> 32); }
                 }
             }
+            if (threadIdx.x >= G && threadIdx.x < 160) hh[threadIdx.x] = 0xFFFFFFFFu;   // padding: never below a head
             __syncthreads();
-            {   // rank of every head among all heads (the order is total, so ranks are distinct): four threads per
-                // head, a quarter of the comparisons each
+            {   // Rank of every head among all heads (the order is total, so ranks are distinct): four threads per
+                // head, a quarter of the comparisons each.  The high word of a key (the ordering score) almost always
+                // decides, so it is compared first, four heads per 128-bit load; only a head whose high word occurs
+                // more than once goes through the full (key, slot) comparison.
                 const uint32_t h = threadIdx.x >> 2, part = threadIdx.x & 3u;
-                uint32_t rank = 0;
+                uint32_t lt = 0, eq = 0;
                 uint64_t mk = kKeySentinel; uint32_t mi = kIdxSentinel;
-                if (h < G) {
-                    mk = hk[h]; mi = hi[h];
-                    const uint32_t q4 = (G + 3) >> 2, j0 = part * q4, j1 = j0 + q4 < G ? j0 + q4 : G;
-                    if (mi != kIdxSentinel) {
-#pragma unroll 4
-                        for (uint32_t j = j0; j < j1; j++) rank += better(hk[j], hi[j], mk, mi) ? 1u : 0u;
+                if (h < G) { mk = hk[h]; mi = hi[h]; }
+                const uint32_t mh = (uint32_t)(mk >> 32);
+                if (h < G && mi != kIdxSentinel) {
+                    const uint4 *h4 = reinterpret_cast<const uint4 *>(hh) + part * 10;   // 160 padded heads / 4 parts
+#pragma unroll
+                    for (int j = 0; j < 10; j++) {
+                        const uint4 v = h4[j];
+                        lt += (v.x < mh) + (v.y < mh) + (v.z < mh) + (v.w < mh);
+                        eq += (v.x == mh) + (v.y == mh) + (v.z == mh) + (v.w == mh);
                     }
                 }
-                rank += __shfl_xor_sync(0xffffffffu, rank, 1);
-                rank += __shfl_xor_sync(0xffffffffu, rank, 2);
+                lt += __shfl_xor_sync(0xffffffffu, lt, 1); eq += __shfl_xor_sync(0xffffffffu, eq, 1);
+                lt += __shfl_xor_sync(0xffffffffu, lt, 2); eq += __shfl_xor_sync(0xffffffffu, eq, 2);
+                uint32_t rank = lt;
+                if (eq > 1) {   // rare: several heads share the high word
+                    rank = 0;
+                    const uint32_t q4 = (G + 3) >> 2, j0 = part * q4, j1 = j0 + q4 < G ? j0 + q4 : G;
+                    for (uint32_t j = j0; j < j1; j++) rank += better(hk[j], hi[j], mk, mi) ? 1u : 0u;
+                    rank += __shfl_xor_sync(0xfu << (threadIdx.x & 28u), rank, 1);
+                    rank += __shfl_xor_sync(0xfu << (threadIdx.x & 28u), rank, 2);
+                }
                 if (h < G && part == 0 && mi != kIdxSentinel && rank == k - 1) { s_tkey = mk; s_tidx = mi; }
                 // fewer than k heads: T stays +inf and every candidate survives
             }
@@ -352,7 +366,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
                 done = true;
                 if (warp == 0) {
                     if (lane < cnt) { key = sk[lane]; idx = si[lane]; }
-                    warp_sort32_rolled(key, idx, lane);
+                    warp_sort32_rolled(key, idx, lane, cnt >= 32 ? 32u : next_pow2(cnt < 2 ? 2 : cnt));
                     if (cnt > 32) {
                         uint64_t k2 = kKeySentinel; uint32_t i2 = kIdxSentinel;
                         if (32 + lane < cnt) { k2 = sk[32 + lane]; i2 = si[32 + lane]; }
