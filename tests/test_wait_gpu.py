@@ -38,12 +38,12 @@ def test_wait_wakes_on_bus_writes_label_writes_and_foreign_writers():
         # nothing happened since the attach's sync: the wait runs out
         t0 = time.perf_counter()
         assert m.wait(60) is False
-        assert 0.05 <= time.perf_counter() - t0 < 0.5
+        assert 0.05 <= time.perf_counter() - t0 < 2.0
         # a write by the bus owner wakes it long before the timeout
         threading.Timer(0.03, lambda: ref.splinter_set(b"doc00000001", b"vv", 2)).start()
         t0 = time.perf_counter()
         assert m.wait(5000) is True
-        assert time.perf_counter() - t0 < 1.0
+        assert time.perf_counter() - t0 < 3.0
         assert m.wait(5000) is True                  # still dirty until the mirror is synced
         st = m.sync()
         assert st.rows_uploaded >= 1
@@ -60,7 +60,7 @@ def test_wait_wakes_on_bus_writes_label_writes_and_foreign_writers():
         p = subprocess.Popen([writer, name, "0", "8", "5", "100"], stdout=subprocess.PIPE, text=True)
         t0 = time.perf_counter()
         assert m.wait(5000) is True
-        assert time.perf_counter() - t0 < 2.0
+        assert time.perf_counter() - t0 < 4.0
         p.communicate()
         m.sync()
         assert m.wait(20) is False
