@@ -218,6 +218,13 @@ int spl_gpu_merge_topk_device(spl_gpu_ctx *ctx, const spl_gpu_result *d_lists, c
                               uint32_t nlists, uint32_t list_stride, uint32_t order, uint32_t k,
                               spl_gpu_result *d_out, uint32_t *d_out_count, void *stream);
 
+/* The same for a batch: d_lists = [nlists][nq][list_stride] records and d_counts = [nlists][nq], exactly what an
+ * all-gather of every GPU's [nq][list_stride] result block delivers; d_out = [nq][out_stride], d_out_counts[nq].
+ * One launch merges all nq queries.  (No counterpart in the reference: it has one address space.) */
+int spl_gpu_merge_topk_batch_device(spl_gpu_ctx *ctx, const spl_gpu_result *d_lists, const uint32_t *d_counts,
+                                    uint32_t nlists, uint32_t nq, uint32_t list_stride, uint32_t order, uint32_t k,
+                                    spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_out_counts, void *stream);
+
 /* Allocation-free variant of the fused single-query scan.  (No counterpart in the reference; it
  * exists only because of how GPU memory is managed.)
  *

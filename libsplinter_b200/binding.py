@@ -19,7 +19,7 @@ LIB_PATH = _HERE / "libsplinter_gpu.so"
 ABI_SYMBOLS = [
     "spl_gpu_attach", "spl_gpu_attach_image", "spl_gpu_open_dense", "spl_gpu_detach", "spl_gpu_get_info",
     "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_wait", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
-    "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device",
+    "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device", "spl_gpu_merge_topk_batch_device",
     "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
 ]
 
@@ -102,6 +102,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_search_device.argtypes = [vp, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_merge_topk_device.restype = C.c_int
     lib.spl_gpu_merge_topk_device.argtypes = [vp, vp, vp, u32, u32, u32, u32, vp, vp, vp]
+    lib.spl_gpu_merge_topk_batch_device.restype = C.c_int
+    lib.spl_gpu_merge_topk_batch_device.argtypes = [vp, vp, vp, u32, u32, u32, u32, u32, vp, u32, vp, vp]
     lib.spl_gpu_scan_noalloc.restype = C.c_int
     lib.spl_gpu_scan_noalloc.argtypes = [vp, vp, vp, vp, u64, u64, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_slot_meta.restype = C.c_int
@@ -249,6 +251,12 @@ class Mirror:
         self._check(self._lib.spl_gpu_merge_topk_device(self._h, C.c_void_p(d_lists), C.c_void_p(d_counts), nlists,
                                                         stride, order, k, C.c_void_p(d_out), C.c_void_p(d_out_count),
                                                         C.c_void_p(stream)))
+
+    def merge_topk_batch_device(self, d_lists, d_counts, nlists, nq, stride, order, k, d_out, out_stride, d_out_counts,
+                                stream=0):
+        self._check(self._lib.spl_gpu_merge_topk_batch_device(self._h, C.c_void_p(d_lists), C.c_void_p(d_counts), nlists, nq,
+                                                              stride, order, k, C.c_void_p(d_out), out_stride,
+                                                              C.c_void_p(d_out_counts), C.c_void_p(stream)))
 
     def last_totals(self, nq=1):
         t = np.zeros(nq, np.uint32)

@@ -1166,7 +1166,21 @@ extern "C" int spl_gpu_merge_topk_device(spl_gpu_ctx *c, const spl_gpu_result *d
     if (k == 0 || k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "merge needs k in 1..%u", SPL_GPU_KMAX_FUSED);
     if (order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order");
     cudaSetDevice(c->device);
-    CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, list_stride, order, k, d_out, d_out_count,
+    CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, 1, list_stride, order, k, d_out, k, d_out_count,
+                                  stream ? (cudaStream_t)stream : c->stream));
+    c->launches++;
+    return 0;
+}
+
+extern "C" int spl_gpu_merge_topk_batch_device(spl_gpu_ctx *c, const spl_gpu_result *d_lists, const uint32_t *d_counts,
+                                               uint32_t nlists, uint32_t nq, uint32_t list_stride, uint32_t order, uint32_t k,
+                                               spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_out_counts, void *stream) {
+    if (!c || !d_lists || !d_counts || !d_out || !d_out_counts) return fail(-2, EINVAL, "null argument");
+    if (k == 0 || k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "merge needs k in 1..%u", SPL_GPU_KMAX_FUSED);
+    if (order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order");
+    if (nq == 0 || out_stride < k) return fail(-2, EINVAL, "merge needs nq >= 1 and out_stride >= k");
+    cudaSetDevice(c->device);
+    CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, nq, list_stride, order, k, d_out, out_stride, d_out_counts,
                                   stream ? (cudaStream_t)stream : c->stream));
     c->launches++;
     return 0;

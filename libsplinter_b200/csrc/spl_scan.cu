@@ -277,22 +277,30 @@ cudaError_t launch_scan_fast(const ScanArgs &a, int grid, cudaStream_t stream) {
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t kMergeMaxEntries = 8192;  // nlists * stride candidates per call (96 KB of smem)
 
+// One CTA per query.  Gathered layout: lists[shard][query][stride] records, counts[shard][query]; with nq = 1 that is
+// simply nlists consecutive lists.  Output: out[query][out_stride], out_count[query].
 __global__ void __launch_bounds__(1024, 1)
-merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t stride,
-                     uint32_t order, uint32_t k, uint32_t entries, spl_gpu_result *out, uint32_t *out_count) {
+merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t nq, uint32_t stride,
+                     uint32_t order, uint32_t k, uint32_t entries, spl_gpu_result *out, uint32_t out_stride,
+                     uint32_t *out_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
     uint32_t *slot = reinterpret_cast<uint32_t *>(keys + entries);
     uint32_t *pos = slot + entries;
+    const uint32_t q = blockIdx.x;
+    out += (size_t)q * out_stride;
+    out_count += q;
     for (uint32_t p = threadIdx.x; p < entries; p += blockDim.x) {
         const uint32_t l = p / stride, i = p - l * stride;
         uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
-        if (l < nlists && i < min(counts[l], stride)) {
-            const spl_gpu_result r = lists[p];
+        uint32_t src = 0;
+        if (l < nlists && i < min(counts[(size_t)l * nq + q], stride)) {
+            src = (uint32_t)(((size_t)l * nq + q) * stride + i);
+            const spl_gpu_result r = lists[src];
             key = make_key(order, r.similarity, r.distance);
             id = r.slot_idx;  // ties between shards break on the GLOBAL slot index
         }
-        keys[p] = key; slot[p] = id; pos[p] = p;
+        keys[p] = key; slot[p] = id; pos[p] = src;
     }
     __syncthreads();
     bitonic_sort_cta(keys, slot, entries, pos);
@@ -311,14 +319,15 @@ cudaError_t merge_prepare() {
     return cudaFuncSetAttribute(merge_results_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kMergeMaxEntries * 16));
 }
 
-cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists,
-                                 uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out,
+cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t nq,
+                                 uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out, uint32_t out_stride,
                                  uint32_t *out_count, cudaStream_t stream) {
     const uint32_t entries = topk_pow2(nlists * stride > k ? nlists * stride : k + 1);
-    if (entries > kMergeMaxEntries) return cudaErrorInvalidValue;
+    if (entries > kMergeMaxEntries || nq == 0) return cudaErrorInvalidValue;
     const size_t smem = (size_t)entries * 16;
     const int threads = entries >= 2048 ? 1024 : (entries >= 512 ? 256 : 128);
-    merge_results_kernel<<<1, threads, smem, stream>>>(lists, counts, nlists, stride, order, k, entries, out, out_count);
+    merge_results_kernel<<<nq, threads, smem, stream>>>(lists, counts, nlists, nq, stride, order, k, entries, out, out_stride,
+                                                       out_count);
     return cudaGetLastError();
 }
 

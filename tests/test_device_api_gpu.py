@@ -97,3 +97,41 @@ def test_batched_mode_through_device_buffers():
         assert np.array_equal(hc, dc)
         for i in range(nq):
             assert host[i][:hc[i]].tobytes() == dev[i][:dc[i]].tobytes()
+
+
+def test_batched_merge_of_gathered_shard_blocks():
+    """[shard][query][k] blocks as an all-gather delivers them -> one launch merges every query; equals the
+    single-store answer per query, and equals the one-query merge entry point."""
+    n, dim, k, shards, nq = 36_000, 768, 10, 3, 7
+    E, bloom, flags = support.synth_dense(91, 99, 0, n, dim)
+    q = support.synth_queries(58, nq, dim)
+    stream = torch.cuda.Stream()
+    with sg.Mirror.open_dense(n, dim) as whole:
+        whole.dense_upload(0, E, bloom, flags)
+        want, wc = whole.search(q, k, bloom_mask=0x3, mode=sg.MODE_FAST)
+    per = n // shards
+    blocks, counts, mirrors = [], [], []
+    try:
+        for s in range(shards):
+            lo, hi = s * per, (n if s == shards - 1 else (s + 1) * per)
+            m = sg.Mirror.open_dense(hi - lo, dim, global_row0=lo)
+            m.dense_upload(0, E[lo:hi], bloom[lo:hi], flags[lo:hi])
+            mirrors.append(m)
+            _, _, d_out, d_cnt = _dev_search(m, q, k, stream, bloom_mask=0x3, mode=sg.MODE_FAST)
+            blocks.append(d_out.reshape(nq * k, 32)); counts.append(d_cnt)
+        gathered = torch.cat(blocks).contiguous()
+        gcnt = torch.cat(counts).contiguous()
+        fin = torch.zeros((nq, k, 32), dtype=torch.uint8, device="cuda")
+        fcnt = torch.zeros(nq, dtype=torch.int32, device="cuda")
+        with torch.cuda.stream(stream):
+            mirrors[0].merge_topk_batch_device(gathered.data_ptr(), gcnt.data_ptr(), shards, nq, k, sg.ORDER_COSINE, k,
+                                               fin.data_ptr(), k, fcnt.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        got = fin.cpu().numpy().view(sg.RESULT_DTYPE).reshape(nq, k)
+        gc = fcnt.cpu().numpy()
+        for i in range(nq):
+            assert gc[i] == wc[i]
+            assert got[i][:gc[i]].tobytes() == want[i][:wc[i]].tobytes()
+    finally:
+        for m in mirrors:
+            m.close()
