@@ -236,17 +236,27 @@ constexpr uint32_t epilogue_scratch_bytes() { return NW * 32 * 12 + NW * kFoldBa
 
 template <int NW>
 __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_t nq, const uint64_t *skeys, const uint32_t *sidx,
-                                                      unsigned char *scratch, uint32_t *s_flag) {
+                                                      unsigned char *scratch, uint32_t *s_flag,
+                                                      const uint32_t *rows_issued = nullptr) {
     const uint32_t k = a.k, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint64_t *xk = reinterpret_cast<uint64_t *>(scratch);
     uint32_t *xi = reinterpret_cast<uint32_t *>(xk + NW * 32);
     uint64_t *fk = reinterpret_cast<uint64_t *>(scratch + NW * 32 * 12);
     uint32_t *fi = reinterpret_cast<uint32_t *>(fk + NW * kFoldBatch * 32);
     __syncthreads();  // lists final, ring idle
+    // a CTA whose producers issued no row at all (a very selective label mask) has nothing to sort or merge
+    const bool cta_empty = rows_issued && *rows_issued == 0;
     // 1 + 2. per query: every warp sorts its list, tree merge, warp 0 publishes the CTA's k best
 #pragma unroll 1
     for (uint32_t qi = 0; qi < nq; qi++) {
         uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
+        if (cta_empty) {
+            if (warp == 0 && lane < k) {
+                Cand c; c.key = key; c.idx = idx; c.pad = 0;
+                a.cta_cands[((size_t)qi * gridDim.x + blockIdx.x) * k + lane] = c;
+            }
+            continue;
+        }
         if (warp < NW && lane < k) { key = skeys[(qi * NW + warp) * k + lane]; idx = sidx[(qi * NW + warp) * k + lane]; }
         if (warp < NW) warp_sort32_rolled(key, idx, lane, next_pow2(k < 2 ? 2 : k));
         cta_tree_merge32_rolled<NW>(key, idx, xk, xi);

@@ -512,7 +512,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
     uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
     uint64_t *ws_keys = reinterpret_cast<uint64_t *>(smem + L.rows_off);
     uint32_t *ws_idx = reinterpret_cast<uint32_t *>(ws_keys + ws_entries);
-    if (NQ > 1 || a.k <= 32) scan_epilogue_compact<kConsumers>(a, NQ, skeys, sidx, smem + L.rows_off, &s_flag);
+    if (NQ > 1 || a.k <= 32) scan_epilogue_compact<kConsumers>(a, NQ, skeys, sidx, smem + L.rows_off, &s_flag, &s_seq);
     else scan_epilogue<kConsumers, false>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 3] = gtime();
 }
