@@ -207,8 +207,9 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     c->m.dim = c->dim;
     // search scratch
     c->scan_grid = c->sm_count * scan_fast_ctas_per_sm(c->dim, 0);
-    if ((rc = dev_alloc(c, &c->d_cands, (size_t)c->scan_grid * SPL_GPU_KMAX_FUSED, false))) return rc;
-    if ((rc = dev_alloc(c, &c->d_counters, 8, true))) return rc;
+    // one k-entry list per CTA and query: up to 4 queries x 256 entries (small batches) per launch
+    if ((rc = dev_alloc(c, &c->d_cands, (size_t)c->scan_grid * SPL_GPU_KMAX_FUSED * 4, false))) return rc;
+    if ((rc = dev_alloc(c, &c->d_counters, 16, true))) return rc;   // chunk, ticket, 4 survivor counts, 3 more tickets
     c->q_cap = 64;
     c->out_cap = 64 * SPL_GPU_KMAX_FUSED;
     if ((rc = dev_alloc(c, &c->d_q, (size_t)c->q_cap * c->dim, false))) return rc;

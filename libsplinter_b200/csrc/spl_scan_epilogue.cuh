@@ -166,7 +166,7 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
 // Same three steps as scan_epilogue_small, written as ROLLED loops around one instance of each building block.
 // The epilogue runs once per CTA, so its instructions are always cold: measured, the time of the unrolled
 // version (~30 KB of straight-line code per query) was mostly instruction fetch, about 0.45 us per KB.
-// Lists of (query qi, warp w) sit at skeys/sidx[(qi*NW + w) * k].  `scratch` (the idle row ring, at least
+// Lists of (query qi, warp w) sit at skeys/sidx[qi*qstride + w*k].  `scratch` (the idle row ring, at least
 // kEpilogueScratchBytes) holds the tree-merge exchange buffer and, in the last CTA, a staging area so that the
 // loads of all published lists of a round are in flight together while the merges run as a rolled loop.
 // Query qi writes a.out + qi*out_stride, a.out_count[qi*count_stride], a.total[qi] (from counters[2 + qi]).
@@ -235,8 +235,8 @@ template <int NW>
 constexpr uint32_t epilogue_scratch_bytes() { return NW * 32 * 12 + NW * kFoldBatch * 32 * 12; }
 
 template <int NW>
-__device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_t nq, const uint64_t *skeys, const uint32_t *sidx,
-                                                      unsigned char *scratch, uint32_t *s_flag,
+__device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_t nq, uint32_t qstride, const uint64_t *skeys,
+                                                      const uint32_t *sidx, unsigned char *scratch, uint32_t *s_flag,
                                                       const uint32_t *rows_issued = nullptr) {
     const uint32_t k = a.k, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint64_t *xk = reinterpret_cast<uint64_t *>(scratch);
@@ -257,7 +257,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
             }
             continue;
         }
-        if (warp < NW && lane < k) { key = skeys[(qi * NW + warp) * k + lane]; idx = sidx[(qi * NW + warp) * k + lane]; }
+        if (warp < NW && lane < k) { key = skeys[qi * qstride + warp * k + lane]; idx = sidx[qi * qstride + warp * k + lane]; }
         if (warp < NW) warp_sort32_rolled(key, idx, lane, next_pow2(k < 2 ? 2 : k));
         cta_tree_merge32_rolled<NW>(key, idx, xk, xi);
         if (warp == 0 && lane < k) {
@@ -446,8 +446,12 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
 // workspace the final merge may use: `ws_entries` (power of two, >= 2*k) entries at ws_keys/ws_idx
 template <int NW, bool SMALL = true>
 __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys, uint32_t *sidx, uint64_t *ws_keys,
-                                              uint32_t *ws_idx, uint32_t ws_entries, uint32_t *s_flag) {
+                                              uint32_t *ws_idx, uint32_t ws_entries, uint32_t *s_flag, uint32_t qi = 0) {
+    // qi: which query of a small batch this call finishes (skeys/sidx already point at that query's lists).  Each
+    // query has its own published-list area, ticket counter (1, then 9, 10, 11), survivor counter (2 + qi) and outputs.
     const uint32_t k = a.k;
+    const uint32_t tix = qi == 0 ? 1u : 8u + qi;
+    Cand *cands_q = a.cta_cands + (size_t)qi * gridDim.x * k;
     if constexpr (SMALL) {
         if (k <= 32) { scan_epilogue_small<NW>(a, skeys, sidx, s_flag); return; }  // registers + shuffles
     }
@@ -455,7 +459,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
     __syncthreads();
     bitonic_sort_cta(skeys, sidx, P);
     {
-        Cand *dst = a.cta_cands + (size_t)blockIdx.x * k;
+        Cand *dst = cands_q + (size_t)blockIdx.x * k;
         for (uint32_t p = threadIdx.x; p < k; p += blockDim.x) {
             Cand c;
             c.key = skeys[p]; c.idx = sidx[p]; c.pad = 0;
@@ -465,7 +469,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
-        const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
+        const uint32_t ticket = atomicAdd(&a.counters[tix], 1u);
         *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
     }
     __syncthreads();
@@ -487,7 +491,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
         if (G <= ws_entries && s <= G) {   // (uniform)
             if (threadIdx.x == 0) { s_cnt2 = 0; s_tk2 = kKeySentinel; s_ti2 = kIdxSentinel; }
             for (uint32_t c = threadIdx.x; c < G; c += blockDim.x) {
-                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + (size_t)c * k + p));
+                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(cands_q + (size_t)c * k + p));
                 ws_keys[c] = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
                 ws_idx[c] = (uint32_t)raw.z;
             }
@@ -504,7 +508,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
             const uint64_t tk = s_tk2; const uint32_t ti = s_ti2;
 #pragma unroll 4
             for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) {
-                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + i));
+                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(cands_q + i));
                 const uint64_t ek = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
                 const uint32_t ei = (uint32_t)raw.z;
                 if (ei != kIdxSentinel && !better(tk, ti, ek, ei)) {   // e <= T
@@ -535,7 +539,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
             const uint32_t src = base + (p - k);
             uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
             if (src < total) {
-                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.cta_cands + src));
+                const int4 raw = __ldcg(reinterpret_cast<const int4 *>(cands_q + src));
                 key = ((uint64_t)(uint32_t)raw.y << 32) | (uint32_t)raw.x;
                 id = (uint32_t)raw.z;
             }
@@ -545,8 +549,9 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
         bitonic_sort_cta(ws_keys, ws_idx, W);  // running top-k stays in [0, k)
     }
     if (threadIdx.x == 0) {
-        if (a.total) *a.total = *reinterpret_cast<volatile uint32_t *>(&a.counters[2]);
-        a.counters[0] = 0; a.counters[1] = 0; a.counters[2] = 0;
+        if (a.total) a.total[qi] = *reinterpret_cast<volatile uint32_t *>(&a.counters[2 + qi]);
+        if (qi == 0) a.counters[0] = 0;   // every CTA is past its scan once any ticket has been taken
+        a.counters[tix] = 0; a.counters[2 + qi] = 0;
     }
     uint32_t cnt = 0;
     for (uint32_t t = threadIdx.x; t < k; t += blockDim.x) {
@@ -558,12 +563,13 @@ __device__ __forceinline__ void scan_epilogue(const ScanArgs &a, uint64_t *skeys
         r.has_embedding = (a.flags[idx] & SPL_ROW_EMB) ? 1u : 0u;
         r.epoch = a.epoch[idx];
         r.bloom = a.bloom[idx];
-        a.out[t] = r;
+        a.out[(size_t)qi * a.out_stride + t] = r;
         // survivors are a prefix of the sorted array: the last valid one knows the count
         if (t + 1 == k || ws_idx[t + 1] == kIdxSentinel) cnt = t + 1;
     }
-    if (cnt) *a.out_count = cnt;
-    else if (threadIdx.x == 0 && ws_idx[0] == kIdxSentinel) *a.out_count = 0;
+    if (cnt) a.out_count[(size_t)qi * a.count_stride] = cnt;
+    else if (threadIdx.x == 0 && ws_idx[0] == kIdxSentinel) a.out_count[(size_t)qi * a.count_stride] = 0;
+    __syncthreads();   // the workspace and *s_flag are reused by the next query of a batch
 }
 
 // sentinel-fill the padded lists region; every scan kernel calls this before its main loop

@@ -124,7 +124,7 @@ __host__ __device__ constexpr bool tma_query_in_smem(uint32_t dim, uint32_t nq) 
 __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32_t nq = 1) {
     TmaLayout L;
     L.row_bytes = dim * 4;
-    L.list_entries = nq == 1 ? scan_topk_entries(k, kConsumers) : nq * kConsumers * k;
+    L.list_entries = nq * scan_topk_entries(k, kConsumers);   // per query: kConsumers lists of k entries, padded to a power of two
     const uint32_t topk = L.list_entries * 12u;                    // u64 keys[] then u32 idx[]
     L.full_off = (topk + 15u) & ~15u;                             // top-k lists sit at offset 0
     L.empty_off = L.full_off + kMaxPairs * 8;
@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const TmaLayout L = tma_layout(a.dim, a.k, NQ);
     const uint32_t list_entries = L.list_entries;
+    const uint32_t qstride = list_entries / NQ;   // list entries per query
     uint64_t *skeys = reinterpret_cast<uint64_t *>(smem);
     uint32_t *sidx = reinterpret_cast<uint32_t *>(skeys + list_entries);
     const uint32_t full0 = smem_u32(smem + L.full_off), empty0 = smem_u32(smem + L.empty_off);
@@ -495,7 +496,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                 uint4 *stp = wstate + cq * kConsumers + warp;
                 const uint4 cs = *stp;   // re-read: an earlier candidate of this pair may have moved the bound
                 WarpTopK T;
-                T.keys = skeys + (cq * kConsumers + warp) * a.k; T.idxs = sidx + (cq * kConsumers + warp) * a.k;
+                T.keys = skeys + cq * qstride + warp * a.k; T.idxs = sidx + cq * qstride + warp * a.k;
                 T.k = a.k; T.cnt = cs.w & 0xffffu; T.thr_pos = cs.w >> 16;
                 T.thr_key = ((uint64_t)cs.y << 32) | cs.x; T.thr_idx = cs.z;
                 if (T.admits(ckey, crow)) {
@@ -512,8 +513,13 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
     uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
     uint64_t *ws_keys = reinterpret_cast<uint64_t *>(smem + L.rows_off);
     uint32_t *ws_idx = reinterpret_cast<uint32_t *>(ws_keys + ws_entries);
-    if (NQ > 1 || a.k <= 32) scan_epilogue_compact<kConsumers>(a, NQ, skeys, sidx, smem + L.rows_off, &s_flag, &s_seq);
-    else scan_epilogue<kConsumers, false>(a, skeys, sidx, ws_keys, ws_idx, ws_entries, &s_flag);
+    if (a.k <= 32) {
+        scan_epilogue_compact<kConsumers>(a, NQ, qstride, skeys, sidx, smem + L.rows_off, &s_flag, &s_seq);
+    } else {
+#pragma unroll 1
+        for (uint32_t qi = 0; qi < NQ; qi++)
+            scan_epilogue<kConsumers, false>(a, skeys + qi * qstride, sidx + qi * qstride, ws_keys, ws_idx, ws_entries, &s_flag, qi);
+    }
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 3] = gtime();
 }
 
@@ -525,7 +531,7 @@ bool scan_tma_supported(uint32_t dim, uint32_t k) {
 // small-batch variant: nq in {2, 4} queries per pass, register/shuffle epilogue only (k <= 32)
 bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq) {
     if (nq != 2 && nq != 4) return false;
-    if (k == 0 || k > 32 || !scan_tma_supported(dim, k)) return false;
+    if (k == 0 || k > 256 || !scan_tma_supported(dim, k)) return false;
     const TmaLayout L = tma_layout(dim, k, nq);
     return L.pairs >= kMinPairs;
 }

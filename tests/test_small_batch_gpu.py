@@ -26,7 +26,7 @@ def corpus():
 
 
 @pytest.mark.parametrize("nq", [2, 3, 4, 5, 7, 8])
-@pytest.mark.parametrize("k", [1, 10, 32])
+@pytest.mark.parametrize("k", [1, 10, 32, 33, 100, 256])
 def test_batch_equals_one_at_a_time_and_the_oracle(corpus, nq, k):
     m, E, bloom, flags, q = corpus
     out, counts = m.search(q[:nq], k, mode=sg.MODE_FAST, bloom_mask=0x1)
