@@ -203,9 +203,12 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         const uint32_t nchunks = (ngroups + cg - 1) / cg;
         auto chunk_g0 = [&](uint32_t c) -> uint32_t { return c * cg; };
         auto chunk_len = [&](uint32_t) -> uint32_t { return cg; };
+        // Every producer warp's FIRST chunk is fixed (CTA * kProducers + producer), so the scan starts without waiting
+        // for an atomic's round trip; the shared counter hands out the chunks after those.
+        const uint32_t first_dynamic = gridDim.x * kProducers;
         auto fetch_chunk = [&]() -> uint32_t {
             uint32_t c = 0;
-            if (lane == 0) c = atomicAdd(&a.counters[0], 1u);
+            if (lane == 0) c = atomicAdd(&a.counters[0], 1u) + first_dynamic;
             return c;  // lane 0 only; broadcast lazily so the atomic's latency is not exposed here
         };
         auto load_chunk_pred = [&](uint32_t c, uint32_t (&f)[kChunk], uint64_t (&b)[kChunk]) {
@@ -266,7 +269,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
                 __syncwarp();
             }
         };
-        uint32_t cA = __shfl_sync(0xffffffffu, fetch_chunk(), 0);
+        uint32_t cA = blockIdx.x * kProducers + (warp - kConsumers);
         uint32_t fA[kChunk], fB[kChunk]; uint64_t bA[kChunk], bB[kChunk];
         load_chunk_pred(cA, fA, bA);
         uint32_t next_raw = fetch_chunk();
