@@ -66,7 +66,12 @@ static void reg_set(const void *base, uint32_t dim) {
         if (g_reg[i].base == base) { g_reg[i].dim = dim; pthread_mutex_unlock(&g_reg_mu); return; }
         if (!g_reg[i].base && free_i < 0) free_i = i;
     }
-    if (free_i >= 0) { g_reg[free_i].base = base; g_reg[free_i].dim = dim; }
+    if (free_i < 0) {   /* table full: the oldest entries belong to images freed long ago -- overwrite round-robin */
+        static int next_victim = 0;
+        free_i = next_victim;
+        next_victim = (next_victim + 1) % REG_MAX;
+    }
+    g_reg[free_i].base = base; g_reg[free_i].dim = dim;
     pthread_mutex_unlock(&g_reg_mu);
 }
 static uint32_t reg_get(const void *base) {

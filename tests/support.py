@@ -199,35 +199,43 @@ def new_image(slots, max_val_sz=64, dim=768) -> np.ndarray:
 
 
 def image_set(img, key, val=b"x"):
+    _register(img)
     return oracle().splo_image_set(_p(img), key.encode(), val, len(val))
 
 
 def image_set_embedding(img, key, vec):
+    _register(img)
     vec = np.ascontiguousarray(vec, np.float32)
     return oracle().splo_image_set_embedding(_p(img), key.encode(), _p(vec))
 
 
 def image_set_label(img, key, mask):
+    _register(img)
     return oracle().splo_image_set_label(_p(img), key.encode(), mask)
 
 
 def image_unset_label(img, key, mask):
+    _register(img)
     return oracle().splo_image_unset_label(_p(img), key.encode(), mask)
 
 
 def image_retrain(img, key):
+    _register(img)
     return oracle().splo_image_retrain(_p(img), key.encode())
 
 
 def image_unset(img, key):
+    _register(img)
     return oracle().splo_image_unset(_p(img), key.encode())
 
 
 def image_find(img, key):
+    _register(img)
     return oracle().splo_image_find(_p(img), key.encode())
 
 
 def image_fill_synthetic(img, nkeys, seed_c=1234, seed_b=99, threads=None):
+    _register(img)
     return oracle().splo_image_fill_synthetic(_p(img), nkeys, seed_c, seed_b, threads or os.cpu_count() or 1)
 
 
