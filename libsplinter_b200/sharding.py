@@ -34,3 +34,22 @@ def gather_lists(local_records: torch.Tensor, local_count: torch.Tensor, world: 
         dist.all_gather_into_tensor(flat, local_records)
         dist.all_gather_into_tensor(counts, local_count)
     return flat.view(world, k, local_records.shape[1]), counts
+
+
+def gather_blocks(local_block: torch.Tensor, local_counts: torch.Tensor, world: int, out_block=None, out_counts=None):
+    """all-gather one rank's batch of results: local_block [nq*k, 32] uint8 (nq record lists of k), local_counts [nq].
+
+    Returns (gathered [world*nq*k, 32], counts [world*nq]) laid out [rank][query][k] / [rank][query] -- the layout
+    spl_gpu_merge_topk_batch_device merges in one launch.  Pass preallocated outputs to avoid per-call allocation."""
+    if out_block is None:
+        out_block = torch.empty((world * local_block.shape[0], local_block.shape[1]), dtype=local_block.dtype,
+                                device=local_block.device)
+    if out_counts is None:
+        out_counts = torch.empty(world * local_counts.shape[0], dtype=local_counts.dtype, device=local_counts.device)
+    if world == 1:
+        out_block.copy_(local_block)
+        out_counts.copy_(local_counts)
+    else:
+        dist.all_gather_into_tensor(out_block, local_block)
+        dist.all_gather_into_tensor(out_counts, local_counts)
+    return out_block, out_counts

@@ -54,6 +54,30 @@ WORKER = textwrap.dedent("""
             full, fc = support.oracle_search_dense(q[qi], Eg, bg, fg, k=K, order=order, bloom_mask=mask)
             ok &= (m == fc[0]) and np.array_equal(out[:m]["idx"], full[0][:m]["idx"]) \\
                 and np.array_equal(out[:m]["similarity"].view(np.uint32), full[0][:m]["similarity"].view(np.uint32))
+    # the batched form: every rank contributes a [nq][K] block, gathered as [rank][query][K]
+    from libsplinter_b200.sharding import gather_blocks
+    ref_local, rc = support.oracle_search_dense(q, E, bloom, flags, k=K, bloom_mask=1)
+    blk = np.zeros((3, K), RESULT_DTYPE)
+    for qi in range(3):
+        n = int(rc[qi])
+        blk[qi]["slot_idx"][:n] = ref_local[qi]["idx"][:n] + lo
+        blk[qi]["similarity"][:n] = ref_local[qi]["similarity"][:n]
+        blk[qi]["distance"][:n] = ref_local[qi]["distance"][:n]
+    gb, gc = gather_blocks(torch.from_numpy(blk.view(np.uint8).reshape(3 * K, 32).copy()),
+                           torch.from_numpy(rc.astype(np.int32)), world)
+    gb = gb.numpy().view(RESULT_DTYPE).reshape(world, 3, K)
+    gc = gc.numpy().reshape(world, 3)
+    Eg, bg, fg = support.synth_dense(1234, 99, 0, N, DIM)
+    full, fc = support.oracle_search_dense(q, Eg, bg, fg, k=K, bloom_mask=1)
+    for qi in range(3):
+        flat = np.zeros((world, K), support.SPLO_RESULT)
+        for w in range(world):
+            flat[w]["idx"] = gb[w, qi]["slot_idx"]; flat[w]["similarity"] = gb[w, qi]["similarity"]
+            flat[w]["distance"] = gb[w, qi]["distance"]
+        out = np.zeros(K, support.SPLO_RESULT)
+        m = support.oracle().splo_merge_topk(support._p(flat), support._p(gc[:, qi].astype(np.uint32).copy()), world, K, 0, K,
+                                             support._p(out))
+        ok &= (m == fc[qi]) and np.array_equal(out[:m]["idx"], full[qi][:m]["idx"])
     flag = torch.tensor([1 if ok else 0])
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

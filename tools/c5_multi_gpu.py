@@ -23,7 +23,7 @@ import torch.distributed as dist
 
 import libsplinter_b200 as sg
 import support
-from libsplinter_b200.sharding import shard_range
+from libsplinter_b200.sharding import gather_blocks, shard_range
 
 slots = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 20
 fill = float(sys.argv[2]) if len(sys.argv) > 2 else 0.5
@@ -91,8 +91,7 @@ try:
 
     def batched_search():
         m.search_device(p, dq.data_ptr(), blk.data_ptr(), K, bcnt.data_ptr(), stream)
-        dist.all_gather_into_tensor(g_blk, blk)
-        dist.all_gather_into_tensor(g_cnt, bcnt)
+        gather_blocks(blk, bcnt, world, g_blk, g_cnt)
         m.merge_topk_batch_device(g_blk.data_ptr(), g_cnt.data_ptr(), world, NQ, K, sg.ORDER_COSINE, K,
                                   fin.data_ptr(), K, fcnt.data_ptr(), stream)
         tstream.synchronize()
