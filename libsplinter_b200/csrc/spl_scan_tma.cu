@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
             }
             {   // passing rows per group seen in this chunk -> length to ask for next (>= 40 %: 2, >= 5 %: 4, else 8)
                 const uint32_t len = c & 15u;
-                const uint32_t pick = T * 10u >= 130u * len ? 2u : (T * 10u >= 16u * len ? 4u : 8u);
+                const uint32_t pick = T * 10u >= 260u * len ? 1u : (T * 10u >= 130u * len ? 2u : (T * 10u >= 16u * len ? 4u : 8u));
                 want = pick < cg ? pick : cg;
             }
             if (T == 0) return;
