@@ -72,21 +72,26 @@ struct WarpTopK {
     __device__ __forceinline__ bool admits(uint64_t key, uint32_t idx) const {
         return cnt < k || better(key, idx, thr_key, thr_idx);
     }
+    // thr := the worst entry (largest key, then largest slot index) and its position.  Each lane finds the worst of
+    // its own entries; the warp-wide maximum is then taken word by word with three REDUX instructions (high word,
+    // low word among the lanes that tie on it, slot index among those) instead of a five-step shuffle tree over
+    // four registers -- this runs after every insertion, and small or selective scans insert a lot.
     __device__ void recompute(uint32_t lane) {
         uint64_t mk = 0; uint32_t mi = 0, mp = 0; bool has = false;
         for (uint32_t p = lane; p < cnt; p += kWarp) {
             uint64_t key = keys[p]; uint32_t id = idxs[p];
             if (!has || better(mk, mi, key, id)) { mk = key; mi = id; mp = p; has = true; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            uint64_t ok = __shfl_xor_sync(0xffffffffu, mk, off);
-            uint32_t oi = __shfl_xor_sync(0xffffffffu, mi, off);
-            uint32_t op = __shfl_xor_sync(0xffffffffu, mp, off);
-            bool oh = __shfl_xor_sync(0xffffffffu, (int)has, off) != 0;
-            if (oh && (!has || better(mk, mi, ok, oi))) { mk = ok; mi = oi; mp = op; has = true; }
-        }
-        thr_key = mk; thr_idx = mi; thr_pos = mp;
+        const uint32_t hi = has ? (uint32_t)(mk >> 32) : 0u;
+        const uint32_t mhi = __reduce_max_sync(0xffffffffu, hi);
+        const bool c1 = has && hi == mhi;
+        const uint32_t lo = c1 ? (uint32_t)mk : 0u;
+        const uint32_t mlo = __reduce_max_sync(0xffffffffu, lo);
+        const bool c2 = c1 && lo == mlo;
+        const uint32_t mid = __reduce_max_sync(0xffffffffu, c2 ? mi : 0u);
+        const unsigned win = __ballot_sync(0xffffffffu, c2 && mi == mid);   // slot indices are unique: one lane
+        thr_key = ((uint64_t)mhi << 32) | mlo; thr_idx = mid;
+        thr_pos = __shfl_sync(0xffffffffu, mp, win ? __ffs(win) - 1 : 0);
     }
     __device__ void insert(uint64_t key, uint32_t idx, uint32_t lane) {
         if (cnt < k) {
