@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define SPL_GPU_ABI_VERSION 1
+#define SPL_GPU_ABI_VERSION 2
 
 typedef struct spl_gpu_ctx spl_gpu_ctx;
 
@@ -110,7 +110,23 @@ typedef struct spl_gpu_sync_stats {
     uint64_t bytes_h2d;
     double   sweep_ms, upload_ms;
     uint64_t header_epoch;   /* H->epoch observed at the start of the sweep */
+    uint64_t rows_revalidated; /* clean rows whose whole content was re-hashed against the store this sweep (1/1024 of
+                                  them per sweep, so every row is looked at in full once per 1024 sweeps) */
+    uint64_t stale_rows_found; /* ... of which differed although {hash, epoch, first cache line} had not moved: re-sent */
 } spl_gpu_sync_stats;
+
+/* Diagnostics accumulated over the life of a context (spl_gpu_get_counters). */
+typedef struct spl_gpu_counters {
+    uint32_t struct_size;    /* = sizeof(spl_gpu_counters), set by the caller */
+    uint32_t reserved;
+    uint64_t batch_queries;  /* queries handed to the bf16 tensor-core path (host- and device-buffer calls) */
+    uint64_t batch_unproven; /* ... of which the host-buffer call re-answered on the fp32 scan because their candidate
+                                list overflowed or the bf16 scores could not prove the selection */
+    uint64_t exact_unproven; /* SPL_MODE_EXACT queries that needed the full exact pass */
+    uint64_t stale_rows_found; /* sum of spl_gpu_sync_stats.stale_rows_found */
+    uint64_t batch_rescored_extra; /* rows the batched path re-scored beyond its fixed 2k per query because their bf16
+                                      score was within the error bound of the k-th (host-buffer calls only) */
+} spl_gpu_counters;
 
 typedef struct spl_gpu_info {
     uint32_t abi_version, dim;
@@ -142,6 +158,7 @@ spl_gpu_ctx *spl_gpu_open_dense(uint64_t n_rows, uint32_t dim, uint64_t global_r
 void spl_gpu_detach(spl_gpu_ctx *ctx);
 
 int  spl_gpu_get_info(const spl_gpu_ctx *ctx, spl_gpu_info *out);
+int  spl_gpu_get_counters(const spl_gpu_ctx *ctx, spl_gpu_counters *out);
 const char *spl_gpu_last_error(void);
 
 /* ---- mirror maintenance ------------------------------------------------------------- */
@@ -150,7 +167,17 @@ const char *spl_gpu_last_error(void);
  * epoch is even and unchanged across the copy (reader rule, splinter.c:598-605); a slot that
  * is busy keeps its previous mirror row and is counted in skipped_busy.  Dirty = cached
  * {hash, epoch, bloom, val_len>0} differs from the slot's (label changes move no slot epoch:
- * splinter.c:843).  May run concurrently with spl_gpu_search from other threads. */
+ * splinter.c:843).
+ *
+ * May run concurrently with spl_gpu_search AND spl_gpu_search_device from other threads, on any stream.  What a
+ * search then sees is the device-side form of the seqlock promise (splinter.h:368-396): every slot is seen either
+ * as it was before or as it is after an update batch -- its embedding row, bf16 shadow, norm, flags, bloom and
+ * epoch always belong to ONE consistent copy of the slot; never a half-written row.  (Different slots may be seen
+ * at different points of the sweep, exactly as a reference reader walking the store sees them.)  The library
+ * enforces this with stream order: update batches run on the context's stream; each waits for the last search
+ * enqueued on another stream, and each search enqueued on another stream waits for the last update batch.
+ * Exception: a search captured into a CUDA graph carries no such dependency -- order graph launches against
+ * spl_gpu_sync yourself. */
 int spl_gpu_sync(spl_gpu_ctx *ctx, spl_gpu_sync_stats *stats /* nullable */);
 
 /* Sleep until the store looks different from the last spl_gpu_sync, or timeout_ms passes.  Replaces a
@@ -206,8 +233,24 @@ int spl_gpu_last_totals(const spl_gpu_ctx *ctx, uint32_t *totals, uint32_t nq);
 
 /* Device-buffer search: d_q / d_out / d_counts are device pointers on the context's device;
  * the launches are enqueued on `stream` (a cudaStream_t; NULL = the context's stream) and the
- * call does not synchronise.  k must be in 1..SPL_GPU_KMAX_FUSED. */
+ * call does not synchronise.  k must be in 1..SPL_GPU_KMAX_FUSED.
+ *
+ * Ordering: the call is ordered on the GPU after every spl_gpu_sync update batch enqueued before it and
+ * before every one enqueued after it (see spl_gpu_sync), and after the previous search of this context
+ * on a different stream (searches of one context share its scratch, so they run one after another
+ * whatever streams they are on; use one context per concurrent search stream for overlap).
+ *
+ * A query the requested mode cannot answer on the device alone never comes back as "0 hits":
+ * d_counts[q] = SPL_GPU_COUNT_UNANSWERED (and its records are undefined) when
+ *   - SPL_MODE_BATCH_BF16 / AUTO->batched: the query's candidate list overflowed, or the bf16 scores
+ *     could not prove that the re-scored candidates contain the true top-k (a crowd of near-duplicates
+ *     inside the bf16 error bound);
+ *   - SPL_MODE_EXACT: the selection proof failed even with the widest candidate margin.
+ * Re-issue such a query with SPL_MODE_FAST (or through spl_gpu_search, which falls back by itself).
+ * spl_gpu_merge_topk_device / _batch_device propagate the marker: a merged query is UNANSWERED when any of
+ * its input lists is. */
 #define SPL_GPU_KMAX_FUSED 256u
+#define SPL_GPU_COUNT_UNANSWERED 0xFFFFFFFFu
 int spl_gpu_search_device(spl_gpu_ctx *ctx, const spl_gpu_search_params *p, const float *d_q,
                           spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, void *stream);
 

@@ -21,6 +21,7 @@ ABI_SYMBOLS = [
     "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_wait", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
     "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device", "spl_gpu_merge_topk_batch_device",
     "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
+    "spl_gpu_get_counters",
 ]
 
 ORDER_COSINE, ORDER_L2 = 0, 1
@@ -29,6 +30,7 @@ OPT_PERSISTENT, OPT_BF16_MIRROR = 0x1, 0x2
 ROW_LIST, ROW_ENUM, ROW_EMB = 0x1, 0x2, 0x4
 NO_SLOT = 0xFFFFFFFF
 KMAX_FUSED = 256
+COUNT_UNANSWERED = 0xFFFFFFFF
 
 
 class Opts(C.Structure):
@@ -47,7 +49,13 @@ class SyncStats(C.Structure):
     _fields_ = [("generation", C.c_uint64), ("slots_swept", C.c_uint64), ("rows_uploaded", C.c_uint64),
                 ("meta_updated", C.c_uint64), ("skipped_busy", C.c_uint64), ("aba_rechecked", C.c_uint64),
                 ("bytes_h2d", C.c_uint64), ("sweep_ms", C.c_double), ("upload_ms", C.c_double),
-                ("header_epoch", C.c_uint64)]
+                ("header_epoch", C.c_uint64), ("rows_revalidated", C.c_uint64), ("stale_rows_found", C.c_uint64)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("reserved", C.c_uint32), ("batch_queries", C.c_uint64),
+                ("batch_unproven", C.c_uint64), ("exact_unproven", C.c_uint64), ("stale_rows_found", C.c_uint64),
+                ("batch_rescored_extra", C.c_uint64)]
 
 
 class Info(C.Structure):
@@ -84,6 +92,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_detach.argtypes = [vp]
     lib.spl_gpu_get_info.restype = C.c_int
     lib.spl_gpu_get_info.argtypes = [vp, C.POINTER(Info)]
+    lib.spl_gpu_get_counters.restype = C.c_int
+    lib.spl_gpu_get_counters.argtypes = [vp, C.POINTER(Counters)]
     lib.spl_gpu_last_error.restype = C.c_char_p
     lib.spl_gpu_last_error.argtypes = []
     lib.spl_gpu_sync.restype = C.c_int
@@ -190,6 +200,11 @@ class Mirror:
         i = Info()
         self._check(self._lib.spl_gpu_get_info(self._h, C.byref(i)))
         return i
+
+    def counters(self) -> Counters:
+        cnt = Counters(C.sizeof(Counters))
+        self._check(self._lib.spl_gpu_get_counters(self._h, C.byref(cnt)))
+        return cnt
 
     def wait(self, timeout_ms: int) -> bool:
         """True when the store moved since the last sync (event bus / H->epoch), False on timeout."""

@@ -402,7 +402,25 @@ __global__ void __launch_bounds__(256) threshold_kernel(const float *__restrict_
     (void)nq;
 }
 
-// per query: sort candidates by t, exact fp32 re-score of the best k', reference order, emit k
+// ---- selection proof: how far a row's true score can sit from what the bf16 tensor-core pass saw ----------------
+// Operands are rounded to bf16 with round-to-nearest: every element moves by at most 2^-8 of itself, so the rounded
+// vector e16 = e + de has |de| <= 2^-8 |e|.  The mirror keeps |de|^2 per row (MirrorPtrs::err2, usually ~0.4 of the
+// worst case) and this kernel computes |dq| of its query, which gives two rigorous bounds that need no assumption
+// on how the rounding errors line up:
+//   L2      | |q - e| - |q16 - e16| |  <=  |dq| + |de|                          (triangle inequality)
+//   cosine  angle(q, e) >= angle(q16, e16) - asin(|dq|/|q|) - asin(|de|/|e16|),  and cos is 1-Lipschitz in the angle
+// On top of that the tensor core accumulates dim products in fp32 (relative error <= dim * 2^-24 of |q16||e16|, taken
+// as 2^-12) and the fp32 scores of the re-score themselves carry the scan's 1e-5 tolerance.
+constexpr uint32_t kRescoreCap = 1024;             // most rows one query may have re-scored
+constexpr float kBf16Unit = 0.00390625f;           // 2^-8
+constexpr float kTcAccRel = 2.44140625e-4f;        // 2^-12
+constexpr float kScanTol = 1e-5f;
+__device__ __forceinline__ float asin_upper(float x) {   // >= asin(x) on [0, 0.5]; "no bound" (pi) beyond
+    return x <= 0.5f ? x * (1.0f + 0.2f * x * x) * 1.00001f : 3.2f;
+}
+
+// per query: sort candidates by t, exact fp32 re-score of the best k', reference order, PROVE that no row left
+// out can belong to the top-k (re-scoring the few more that could), emit k
 __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, const float *__restrict__ q32, uint32_t k,
                                                            uint32_t kprime, spl_gpu_result *__restrict__ out,
                                                            uint32_t out_stride, uint32_t *__restrict__ out_count,
@@ -410,8 +428,8 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t total = a.cand_cnt[q];
-    if (total > a.cand_cap) {  // threshold too loose for this query: the host re-runs it on the fp32 scan
-        if (threadIdx.x == 0) { overflow[q] = 1; out_count[q] = 0; }
+    if (total > a.cand_cap) {  // threshold too loose for this query: the fp32 scan answers it
+        if (threadIdx.x == 0) { overflow[q] = 1; out_count[q] = SPL_GPU_COUNT_UNANSWERED; }
         return;
     }
     const uint32_t P = next_pow2(total < 2 ? 2 : total);
@@ -424,24 +442,32 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
     }
     __syncthreads();
     bitonic_sort_cta(keys, idx, P);
-    const uint32_t m = total < kprime ? total : kprime;   // candidates to re-score
-    __shared__ uint64_t rk[512];
-    __shared__ uint32_t ri[512];
+    const uint32_t m = total < kprime ? total : kprime;   // candidates re-scored unconditionally
+    __shared__ uint64_t rk[kRescoreCap];
+    __shared__ uint32_t ri[kRescoreCap];
+    __shared__ uint32_t s_extra, s_fail, s_nout;
     const uint32_t R = next_pow2(m < 2 ? 2 : m);
-    for (uint32_t i = threadIdx.x; i < R; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = kIdxSentinel; }
+    for (uint32_t i = threadIdx.x; i < R; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = i < m ? idx[i] : kIdxSentinel; }
+    if (threadIdx.x == 0) { s_extra = 0; s_fail = 0; }
     __syncthreads();
-    // Exact fp32 re-score of the m best.  Each row is 4*dim bytes somewhere in HBM: the loop is written so that a
-    // warp has two whole rows (2 x dim/128 independent 16-byte loads per lane) in flight at a time -- with scalar
-    // loads in a rolled loop this step was latency-bound and took longer than everything else in the kernel.
+    // Exact fp32 re-score.  Each row is 4*dim bytes somewhere in HBM: the loop is written so that a warp has two
+    // whole rows (2 x dim/128 independent 16-byte loads per lane) in flight at a time -- with scalar loads in a
+    // rolled loop this step was latency-bound and took longer than everything else in the kernel.
     // Same per-lane arithmetic order for every row, so equal rows get equal scores.
     const float4 *qv4 = reinterpret_cast<const float4 *>(q32 + (size_t)q * a.dim);
     const uint32_t nv = a.dim >> 2;  // float4s per row; dim is a multiple of 64 on this path
-    float ma = 0.f;
+    float ma = 0.f, mq16 = 0.f, dq2 = 0.f;   // |q|^2, |bf16(q)|^2, |q - bf16(q)|^2
     for (uint32_t d = lane; d < nv; d += 32) {
         const float4 y = qv4[d];
         ma = fmaf(y.x, y.x, ma); ma = fmaf(y.y, y.y, ma); ma = fmaf(y.z, y.z, ma); ma = fmaf(y.w, y.w, ma);
+        const float yy[4] = { y.x, y.y, y.z, y.w };
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float h = __bfloat162float(__float2bfloat16_rn(yy[j])), e = yy[j] - h;
+            mq16 = fmaf(h, h, mq16); dq2 = fmaf(e, e, dq2);
+        }
     }
-    ma = warp_sum(ma);
+    ma = warp_sum(ma); mq16 = warp_sum(mq16); dq2 = warp_sum(dq2);
     auto score_row = [&](const float4 *e4, float &dot, float &mb, float &ss) {
         dot = 0.f; mb = 0.f; ss = 0.f;
 #pragma unroll 8
@@ -458,24 +484,105 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
         dot = warp_sum(dot); mb = warp_sum(mb); ss = warp_sum(ss);
         float sim = cosine_from_sums(dot, ma, mb), dist = __fsqrt_rn(ss);
         if (!(a.flags[row] & SPL_ROW_EMB)) { sim = 0.f; dist = FLT_MAX; }
-        if (lane == 0) { rk[c] = make_key(a.order, sim, dist); ri[c] = row; }
+        if (lane == 0) rk[c] = make_key(a.order, sim, dist);
     };
     const uint32_t nwarps = blockDim.x / 32;
-    for (uint32_t c = warp; c < m; c += 2 * nwarps) {
-        const uint32_t c2 = c + nwarps;
-        const bool two = c2 < m;
-        const uint32_t row0 = idx[c], row1 = two ? idx[c2] : row0;
-        float d0, b0, s0, d1, b1, s1;
-        score_row(reinterpret_cast<const float4 *>(a.E + (size_t)row0 * a.dim), d0, b0, s0);
-        score_row(reinterpret_cast<const float4 *>(a.E + (size_t)row1 * a.dim), d1, b1, s1);
-        emit(c, row0, d0, b0, s0);
-        if (two) emit(c2, row1, d1, b1, s1);
-    }
+    auto rescore = [&](uint32_t lo, uint32_t hi) {   // rows ri[lo..hi) -> rk[lo..hi)
+        for (uint32_t c = lo + warp; c < hi; c += 2 * nwarps) {
+            const uint32_t c2 = c + nwarps;
+            const bool two = c2 < hi;
+            const uint32_t row0 = ri[c], row1 = two ? ri[c2] : row0;
+            float d0, b0, s0, d1, b1, s1;
+            score_row(reinterpret_cast<const float4 *>(a.E + (size_t)row0 * a.dim), d0, b0, s0);
+            score_row(reinterpret_cast<const float4 *>(a.E + (size_t)row1 * a.dim), d1, b1, s1);
+            emit(c, row0, d0, b0, s0);
+            if (two) emit(c2, row1, d1, b1, s1);
+        }
+    };
+    rescore(0, m);
     __syncthreads();
     bitonic_sort_cta(rk, ri, R);
+
+    // ---- selection proof ----------------------------------------------------------------------------------------
+    // X = the k-th best exact score so far (or the threshold, whichever is harder to beat).  A row that was not
+    // re-scored can only matter if its true score could reach X; its bf16 ordering value bounds its true score
+    // (bounds above).  Every such row still in the candidate list is re-scored now -- X can only get better by
+    // that, so one round is enough -- and rows that never made the list are covered through the list's bound thr.
+    const bool cosine = a.order == SPL_ORDER_COSINE;
+    const bool have_k = m >= k;
+    float simk = 0.f, distk = 0.f;
+    if (have_k) split_key(a.order, rk[k - 1], simk, distk);
+    const float qn = sqrtf(ma), qn16 = sqrtf(mq16), dqn = sqrtf(dq2) * 1.000001f;
+    float S = have_k ? simk : -INFINITY;          // cosine: a row matters only if its similarity can reach S
+    if (a.min_sim > 0.f) S = fmaxf(S, a.min_sim);
+    float Dk = have_k ? distk : INFINITY;         // L2: ... only if its distance can get down to Dk
+    if (a.max_dist > 0.f) Dk = fminf(Dk, a.max_dist);
+    const float DkUp = Dk * (1.0f + kScanTol);
+    const float thq = qn > 0.f ? asin_upper(dqn / qn) : 3.2f;
+    for (uint32_t c = m + threadIdx.x; c < total; c += blockDim.x) {
+        const uint32_t row = idx[c];
+        const float t = ord2f((uint32_t)keys[c]);
+        bool excluded;
+        if (!(a.flags[row] & SPL_ROW_EMB)) {       // scores are exactly (0, FLT_MAX): _search.c:388-391
+            excluded = cosine ? (0.f < S) : (FLT_MAX > DkUp);
+        } else {
+            const float n2 = a.norm2[row], er2 = a.err2[row];
+            const float en16 = sqrtf(n2), de = sqrtf(er2) * 1.000001f;
+            if (cosine) {
+                float sim_up;
+                if (n2 == 0.f && er2 == 0.f) sim_up = 0.f;                    // a zero row scores exactly 0
+                else if (!(qn16 > 0.f) || en16 <= 2.f * de) sim_up = INFINITY;  // no usable bound
+                else sim_up = -t / qn16 + thq + asin_upper(de / en16) + kTcAccRel + kScanTol;
+                excluded = sim_up < S;
+            } else {
+                const float C = t + mq16;                                      // |q16 - e16|^2 as the pass computed it
+                const float delta = 2.f * kTcAccRel * qn16 * en16 + 1e-5f * (n2 + mq16);
+                const float lo = sqrtf(fmaxf(0.f, C - delta)) * (1.0f - 1e-6f) - (dqn + de) * (1.0f + kScanTol);
+                excluded = lo > DkUp;
+            }
+        }
+        if (!excluded) {
+            const uint32_t pos = atomicAdd(&s_extra, 1u);
+            if (m + pos < kRescoreCap) ri[m + pos] = row;   // (slots >= R are written here for the first time)
+        }
+    }
+    if (threadIdx.x == 0 && a.thr[q] < INFINITY) {
+        // rows that never entered the list have an ordering value >= thr
+        const float thr = a.thr[q];
+        bool ok;
+        if (cosine) {
+            const float sim_up = qn16 > 0.f ? -thr / qn16 + thq + asin_upper(kBf16Unit) + kTcAccRel + kScanTol : INFINITY;
+            ok = sim_up < S;
+        } else {
+            // |e16| of an unknown row: at most the shard's maximum, and a row with |e| > Dk + |q| is farther than Dk anyway
+            float emax = sqrtf(__uint_as_float(*a.norm2_max));
+            if (Dk < INFINITY) emax = fminf(emax, 1.004f * (Dk + qn));
+            const float de = kBf16Unit * 1.004f * emax;
+            const float delta = 2.f * kTcAccRel * qn16 * emax + 1e-5f * (emax * emax + mq16);
+            const float lo = sqrtf(fmaxf(0.f, thr + mq16 - delta)) * (1.0f - 1e-6f) - (dqn + de) * (1.0f + kScanTol);
+            ok = lo > DkUp;
+        }
+        if (!ok) s_fail = 1;
+    }
+    __syncthreads();
+    const uint32_t extra = s_extra;
+    if (s_fail || m + extra > kRescoreCap) {
+        // too many near-ties inside the bf16 error bound (or a bound that does not clear): the fp32 scan answers it
+        if (threadIdx.x == 0) { overflow[q] = 1; out_count[q] = SPL_GPU_COUNT_UNANSWERED; }
+        return;
+    }
+    const uint32_t m2 = m + extra;
+    if (extra) {
+        const uint32_t R2 = next_pow2(m2);
+        for (uint32_t i = m2 + threadIdx.x; i < R2; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = kIdxSentinel; }
+        for (uint32_t i = R + threadIdx.x; i < m2; i += blockDim.x) rk[i] = kKeySentinel;   // filled by the re-score below
+        __syncthreads();
+        rescore(m, m2);
+        __syncthreads();
+        bitonic_sort_cta(rk, ri, R2);
+    }
     // threshold on the ordering score (_search.c:398-399): the rows that fail are the tail of the sorted list
-    __shared__ uint32_t s_nout;
-    if (threadIdx.x == 0) s_nout = m < k ? m : k;
+    if (threadIdx.x == 0) { s_nout = m2 < k ? m2 : k; overflow[q] = extra << 1; }
     __syncthreads();
     if (a.min_sim > 0.f || a.max_dist > 0.f) {
         const uint32_t lim = s_nout;

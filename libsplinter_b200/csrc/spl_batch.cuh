@@ -14,6 +14,8 @@ struct BatchArgs {
     const float *E;               // fp32 rows (exact re-score)
     const __nv_bfloat16 *E16;     // bf16 shadow rows (tensor-core operand)
     const float *norm2;           // |bf16(e)|^2
+    const float *err2;            // |e - bf16(e)|^2 (selection proof)
+    const uint32_t *norm2_max;    // float bits of an upper bound of max |bf16(e)|^2 over the shard
     const uint64_t *bloom;
     const uint8_t *flags;
     const uint64_t *epoch;
@@ -47,8 +49,10 @@ struct BatchScratchLayout {
 cudaError_t batch_prepare();  // once per device
 bool batch_supported(uint32_t dim, uint32_t k);
 size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, BatchScratchLayout *L);
-// enqueues: query prep, sampling pass, thresholds, full pass, select + exact re-rank.  d_counts[q] and the
-// flag array returned in *d_overflow_out tell which queries overflowed their candidate list.
+// enqueues: query prep, sampling pass, thresholds, full pass, select + exact re-rank with its selection proof.
+// d_counts[q] = SPL_GPU_COUNT_UNANSWERED and bit 0 of the flag array returned in *d_overflow_out mark the queries
+// the bf16 pass could not answer (list overflow / unprovable selection); the other bits of a flag word hold the
+// number of rows re-scored beyond k' (<< 1).
 cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, unsigned char *scratch, const float *d_q32,
                          uint32_t k, int sm_count, spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts,
                          uint32_t **d_overflow_out, uint32_t *launches, cudaStream_t s);

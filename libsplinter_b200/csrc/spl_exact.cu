@@ -149,6 +149,8 @@ __global__ void __launch_bounds__(32) exact_rescore_kernel(const ExactArgs a) {
             else valid = (kd < wd - kExactDistRel * wd) ? 1u : 0u;
         }
         *a.valid = valid;
+        // device-buffer callers have only the count to go by: an unproven selection must not read as an answer
+        if (!valid) *a.out_count = SPL_GPU_COUNT_UNANSWERED;
     }
 }
 

@@ -96,6 +96,8 @@ struct spl_gpu_ctx {
     std::vector<uint8_t> c_flags;   // SPL_ROW_* incl. EMB
     std::vector<uint8_t> c_state;   // bit0: mirrored at least once, bit1: mirrored row is non-zero
     std::vector<uint64_t> c_fp;     // fingerprint of the mirrored row's first 64 bytes (epoch-ABA detector)
+    std::vector<uint64_t> c_full;   // hash of the whole mirrored row (periodic re-validation of clean rows)
+    uint64_t sweep_no = 0;
     uint64_t c_header_epoch = 0;
     bool first_sync = true;
     int bus_fd = -1;               // this process's duplicate of the owner's eventfd (spl_gpu_wait)
@@ -139,6 +141,17 @@ struct spl_gpu_ctx {
     uint32_t bout_cap = 0;
     // bookkeeping
     std::mutex mu;  // serialises enqueueing on `stream` and the scratch above
+    std::mutex sweep_mu;  // one sweep at a time per context keeps the host caches single-writer
+    // GPU-side ordering between mirror updates (always on `stream`) and searches (on `stream` or a caller's stream):
+    // the seqlock's guarantee carried onto the device.  ev_flush = the last scatter enqueued; ev_search = the last
+    // search enqueued on search_stream.  Searches also share the scratch above, so consecutive searches on different
+    // streams are chained through ev_search as well.
+    cudaEvent_t ev_flush = nullptr, ev_search = nullptr;
+    bool flush_recorded = false, search_recorded = false;
+    cudaStream_t search_stream = nullptr;
+    bool counters_dirty = false;   // a failed call may have left d_counters non-zero: re-zero before the next scan
+    bool totals_valid = false;     // spl_gpu_last_totals: false after a search path that does not count survivors
+    std::atomic<uint64_t> n_batch_queries{0}, n_batch_unproven{0}, n_exact_unproven{0}, n_stale_rows{0}, n_batch_extra{0};
     std::atomic<uint64_t> launches{0};
     bool force_ldg = false;
     bool no_multi = false;  // developer knob SPL_GPU_SCAN_MULTI=0: one query per launch even for small batches
@@ -169,6 +182,8 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreate(&c->ev0));
     CUDA_TRY(cudaEventCreate(&c->ev1));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_flush, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_search, cudaEventDisableTiming));
     CUDA_TRY(scan_tma_prepare());
     CUDA_TRY(batch_prepare());
     CUDA_TRY(merge_prepare());
@@ -203,6 +218,8 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     if (bf16 && c->dim % kE16TileK == 0) {  // the tiled bf16 shadow needs whole 64-element k-blocks
         if ((rc = dev_alloc(c, &c->m.E16, e16_padded_rows(c->n) * c->dim, true))) return rc;
         if ((rc = dev_alloc(c, &c->m.norm2, c->n, true))) return rc;
+        if ((rc = dev_alloc(c, &c->m.err2, c->n, true))) return rc;
+        if ((rc = dev_alloc(c, &c->m.norm2_max, 1, true))) return rc;
     }
     c->m.dim = c->dim;
     // search scratch
@@ -255,8 +272,9 @@ static void destroy(spl_gpu_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->search_recorded) cudaEventSynchronize(c->ev_search);   // a caller-stream search may still read the mirror
     cudaFree(c->m.E); cudaFree(c->m.bloom); cudaFree(c->m.flags); cudaFree(c->m.epoch);
-    cudaFree(c->m.E16); cudaFree(c->m.norm2);
+    cudaFree(c->m.E16); cudaFree(c->m.norm2); cudaFree(c->m.err2); cudaFree(c->m.norm2_max);
     cudaFree(c->d_cands); cudaFree(c->d_counters); cudaFree(c->d_q); cudaFree(c->d_out); cudaFree(c->d_count);
     cudaFree(c->d_exact); cudaFreeHost(c->h_xvalid);
     cudaFree(c->d_batch); cudaFree(c->d_qbatch); cudaFree(c->d_bout); cudaFree(c->d_bcount);
@@ -269,6 +287,8 @@ static void destroy(spl_gpu_ctx *c) {
     }
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_flush) cudaEventDestroy(c->ev_flush);
+    if (c->ev_search) cudaEventDestroy(c->ev_search);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->bus_fd >= 0) close(c->bus_fd);
     if (c->own_map && c->base) munmap((void *)c->base, c->map_size);
@@ -308,7 +328,7 @@ static spl_gpu_ctx *attach_common(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     c->sync_threads = o ? o->sync_threads : 0;
     if (device_setup(c, o) || alloc_mirror(c, o && (o->flags & SPL_OPT_BF16_MIRROR))) { destroy(c); return nullptr; }
     c->c_hash.assign(c->n, 0); c->c_epoch.assign(c->n, 0); c->c_bloom.assign(c->n, 0);
-    c->c_flags.assign(c->n, 0); c->c_state.assign(c->n, 0); c->c_fp.assign(c->n, 0);
+    c->c_flags.assign(c->n, 0); c->c_state.assign(c->n, 0); c->c_fp.assign(c->n, 0); c->c_full.assign(c->n, 0);
     if (spl_gpu_sync(c, nullptr) != 0) { destroy(c); return nullptr; }
     return c;
 }
@@ -338,8 +358,8 @@ extern "C" spl_gpu_ctx *spl_gpu_attach_image(const void *base, size_t size, cons
 }
 
 extern "C" spl_gpu_ctx *spl_gpu_open_dense(uint64_t n_rows, uint32_t dim, uint64_t global_row0, const spl_gpu_opts *o) {
-    if (n_rows == 0 || n_rows > 0xFFFFFFF0ull || dim == 0 || dim % 4) {
-        fail(-2, EINVAL, "dense shard needs 0 < rows < 2^32 and dim %% 4 == 0");
+    if (n_rows == 0 || n_rows > 0xFFFFFFE0ull || dim == 0 || dim % 4) {   // 32-row groups are counted in 32 bits
+        fail(-2, EINVAL, "dense shard needs 0 < rows <= 2^32-32 and dim %% 4 == 0");
         return nullptr;
     }
     spl_gpu_ctx *c = new spl_gpu_ctx();
@@ -400,8 +420,21 @@ extern "C" int spl_gpu_slot_meta(const spl_gpu_ctx *c, uint32_t slot_idx, char k
 
 extern "C" int spl_gpu_last_totals(const spl_gpu_ctx *c, uint32_t *totals, uint32_t nq) {
     if (!c || !totals) return fail(-2, EINVAL, "null argument");
+    if (!c->totals_valid)
+        return fail(-1, ENODATA, "the last search on this context took the batched tensor-core path, which does not count survivors");
     if (nq > kMaxBatchQ) nq = kMaxBatchQ;
     memcpy(totals, c->h_total, (size_t)nq * sizeof(uint32_t));
+    return 0;
+}
+
+extern "C" int spl_gpu_get_counters(const spl_gpu_ctx *c, spl_gpu_counters *out) {
+    if (!c || !out) return fail(-2, EINVAL, "null argument");
+    if (out->struct_size != sizeof(spl_gpu_counters)) return fail(-2, EINVAL, "spl_gpu_counters size mismatch");
+    out->batch_queries = c->n_batch_queries.load();
+    out->batch_unproven = c->n_batch_unproven.load();
+    out->exact_unproven = c->n_exact_unproven.load();
+    out->stale_rows_found = c->n_stale_rows.load();
+    out->batch_rescored_extra = c->n_batch_extra.load();
     return 0;
 }
 
@@ -417,14 +450,58 @@ extern "C" double spl_gpu_last_scan_ms(const spl_gpu_ctx *c) { return c ? c->las
 // sync
 // ------------------------------------------------------------------------------------------------
 struct SyncCounters {
-    std::atomic<uint64_t> rows{0}, meta{0}, busy{0}, aba{0}, bytes{0};
+    std::atomic<uint64_t> rows{0}, meta{0}, busy{0}, aba{0}, bytes{0}, reval{0}, stale{0};
     std::atomic<int> err{0};
 };
+
+// ---- GPU-side ordering of mirror updates against searches ---------------------------------------------------------
+// The reference's reader never returns a half-written slot (seqlock, splinter.c:598-605).  On the device the same
+// promise needs stream order: a scatter kernel must not rewrite a row (its fp32 copy, bf16 shadow, norm, flags,
+// bloom) while a scan on ANOTHER stream is reading it, and the next scan must see the scatter complete.  All three
+// helpers are called with c->mu held.  A stream that is being captured into a CUDA graph is left alone: events
+// recorded there would not order anything outside the graph, so such a caller orders graph launches against
+// spl_gpu_sync itself.
+static bool stream_capturing(cudaStream_t s) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); return false; }
+    return st != cudaStreamCaptureStatusNone;
+}
+
+// before a mirror update is enqueued on c->stream: wait for the last search if it ran elsewhere
+static int order_before_update(spl_gpu_ctx *c) {
+    if (c->search_recorded && c->search_stream != c->stream) CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_search, 0));
+    return 0;
+}
+static int order_after_update(spl_gpu_ctx *c) {
+    CUDA_TRY(cudaEventRecord(c->ev_flush, c->stream));
+    c->flush_recorded = true;
+    return 0;
+}
+// before a search is enqueued on s: wait for the last mirror update (if s is not the update stream) and for the
+// last search on a different stream (they share the context's scratch: candidate lists, counters, batch lists)
+static int order_before_search(spl_gpu_ctx *c, cudaStream_t s) {
+    if (stream_capturing(s)) return 0;
+    if (s != c->stream && c->flush_recorded) CUDA_TRY(cudaStreamWaitEvent(s, c->ev_flush, 0));
+    if (c->search_recorded && c->search_stream != s) CUDA_TRY(cudaStreamWaitEvent(s, c->ev_search, 0));
+    if (c->counters_dirty) {
+        CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(uint32_t), s));
+        c->counters_dirty = false;
+    }
+    return 0;
+}
+static int order_after_search(spl_gpu_ctx *c, cudaStream_t s) {
+    if (stream_capturing(s)) return 0;
+    CUDA_TRY(cudaEventRecord(c->ev_search, s));
+    c->search_recorded = true;
+    c->search_stream = s;
+    return 0;
+}
 
 static int flush_buf(spl_gpu_ctx *c, StageBuf &b, bool rows, SyncCounters &sc) {
     if (b.n == 0) return 0;
     std::lock_guard<std::mutex> lk(c->mu);
     const size_t row_bytes = (size_t)c->dim * 4;
+    if (order_before_update(c)) return -1;
     if (rows) {
         CUDA_TRY(cudaMemcpyAsync(b.d_rows, b.h_rows, (size_t)b.n * row_bytes, cudaMemcpyHostToDevice, c->stream));
         CUDA_TRY(cudaMemcpyAsync(b.d_meta, b.h_meta, (size_t)b.n * sizeof(StagedMeta), cudaMemcpyHostToDevice, c->stream));
@@ -437,6 +514,7 @@ static int flush_buf(spl_gpu_ctx *c, StageBuf &b, bool rows, SyncCounters &sc) {
     }
     c->launches++;
     CUDA_TRY(cudaEventRecord(b.ev, c->stream));
+    if (order_after_update(c)) return -1;
     b.in_flight = true;
     b.n = 0;
     return 0;
@@ -471,12 +549,26 @@ static inline uint64_t row_fingerprint(const uint8_t *p) {
     return h;
 }
 
-static bool row_is_zero(const uint8_t *p, size_t bytes) {
+// one pass over a row: 64-bit hash of all its bytes + "is it all zero"
+static inline uint64_t row_hash(const uint8_t *p, size_t bytes, bool *is_zero) {
     const uint64_t *w = reinterpret_cast<const uint64_t *>(p);
-    uint64_t acc = 0;
-    for (size_t i = 0; i < bytes / 8; i++) acc |= w[i];
-    return acc == 0;
+    uint64_t h0 = 0x9E3779B97F4A7C15ull, h1 = 0xD1342543DE82EF95ull, acc = 0;
+    size_t i = 0;
+    for (; i + 1 < bytes / 8; i += 2) {   // two independent chains keep the multiplier pipelined
+        acc |= w[i] | w[i + 1];
+        h0 = (h0 ^ w[i]) * 0xBF58476D1CE4E5B9ull; h0 ^= h0 >> 32;
+        h1 = (h1 ^ w[i + 1]) * 0x94D049BB133111EBull; h1 ^= h1 >> 32;
+    }
+    for (; i < bytes / 8; i++) { acc |= w[i]; h0 = (h0 ^ w[i]) * 0xBF58476D1CE4E5B9ull; h0 ^= h0 >> 32; }
+    if (is_zero) *is_zero = acc == 0;
+    return h0 ^ (h1 * 0x9E3779B97F4A7C15ull);
 }
+
+// Every sweep re-validates 1/kRevalEvery of the rows it believes clean by hashing the whole row in the store and
+// comparing with the hash taken when the row was mirrored.  That bounds the life of a stale row that slipped past
+// both {hash, epoch} and the first-line fingerprint (a rewrite that restores the epoch and keeps the first 16 floats)
+// to kRevalEvery sweeps, at a cost of n/kRevalEvery row reads per sweep.
+constexpr uint64_t kRevalEvery = 1024;
 
 // Sweep threads pull fixed-size slot ranges from a shared counter: on a host whose cores are also running
 // the store's writers a static split would wait for whichever thread shares a core with one of them.
@@ -486,7 +578,7 @@ static inline uint64_t sweep_chunk(const spl_gpu_ctx *c) {
 }
 
 static void sync_worker(spl_gpu_ctx *c, unsigned tid, std::atomic<uint64_t> *next_chunk, bool header_moved,
-                        SyncCounters *scp) {
+                        uint64_t reval_phase, SyncCounters *scp) {
     using namespace layout;
     SyncCounters &sc = *scp;
     cudaSetDevice(c->device);
@@ -523,6 +615,13 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, std::atomic<uint64_t> *nex
             // once H->epoch has moved.  Compare a fingerprint of the row's first cache line (it sits right
             // behind the metadata line this sweep reads anyway); a scrub or a re-embedding changes it.
             if (row_fingerprint(sl + S_EMBED) != c->c_fp[r]) { row_dirty = true; sc.aba++; }
+        }
+        if (!row_dirty && h != 0 && !(e1 & 1) && ((r ^ reval_phase) & (kRevalEvery - 1)) == 0) {
+            sc.reval++;
+            const uint64_t fh = row_hash(sl + S_EMBED, row_bytes, nullptr);
+            std::atomic_thread_fence(std::memory_order_acquire);
+            // (an epoch that moved while hashing is an ordinary dirty row for the next sweep)
+            if (ld_acq64(sl + S_EPOCH) == e1 && fh != c->c_full[r]) { row_dirty = true; sc.stale++; }
         }
         if (!row_dirty) {
             // label changes move no slot epoch (splinter.c:843): compare bloom + validity bits
@@ -584,7 +683,9 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, std::atomic<uint64_t> *nex
         b.h_meta[b.n] = StagedMeta{ bloom, es, (uint32_t)r, f };
         b.n++;
         c->c_hash[r] = hh; c->c_epoch[r] = es; c->c_bloom[r] = bloom; c->c_flags[r] = f;
-        c->c_state[r] = 1 | (row_is_zero(reinterpret_cast<const uint8_t *>(dst), row_bytes) ? 0 : 2);
+        bool zero_row = false;
+        c->c_full[r] = row_hash(reinterpret_cast<const uint8_t *>(dst), row_bytes, &zero_row);
+        c->c_state[r] = 1 | (zero_row ? 0 : 2);
         c->c_fp[r] = row_fingerprint(reinterpret_cast<const uint8_t *>(dst));
         sc.rows++;
         if (b.n == b.cap) {
@@ -600,8 +701,7 @@ static void sync_worker(spl_gpu_ctx *c, unsigned tid, std::atomic<uint64_t> *nex
 extern "C" int spl_gpu_sync(spl_gpu_ctx *c, spl_gpu_sync_stats *stats) {
     if (!c) return fail(-2, EINVAL, "null context");
     if (c->dense) return fail(-2, EINVAL, "dense contexts have no backing store to sync");
-    static std::mutex sync_mu;  // one sweep at a time per process keeps the host caches single-writer
-    std::lock_guard<std::mutex> sweep_lock(sync_mu);
+    std::lock_guard<std::mutex> sweep_lock(c->sweep_mu);  // per context: several GPUs' sweeps run side by side
     auto t0 = std::chrono::steady_clock::now();
     const uint64_t hdr_epoch = ld_acq64(c->base + layout::H_EPOCH);
     const bool header_moved = c->first_sync || hdr_epoch != c->c_header_epoch;
@@ -609,7 +709,8 @@ extern "C" int spl_gpu_sync(spl_gpu_ctx *c, spl_gpu_sync_stats *stats) {
     const unsigned T = c->sync_threads;
     std::vector<std::thread> th;
     std::atomic<uint64_t> next_chunk{0};
-    for (unsigned t = 0; t < T; t++) th.emplace_back(sync_worker, c, t, &next_chunk, header_moved, &sc);
+    const uint64_t reval_phase = c->sweep_no++;
+    for (unsigned t = 0; t < T; t++) th.emplace_back(sync_worker, c, t, &next_chunk, header_moved, reval_phase, &sc);
     for (auto &x : th) x.join();
     auto t1 = std::chrono::steady_clock::now();
     if (sc.err.load()) return fail(-1, EIO, "sync worker failed while staging rows to the device");
@@ -632,7 +733,10 @@ extern "C" int spl_gpu_sync(spl_gpu_ctx *c, spl_gpu_sync_stats *stats) {
         stats->sweep_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
         stats->upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
         stats->header_epoch = hdr_epoch;
+        stats->rows_revalidated = sc.reval;
+        stats->stale_rows_found = sc.stale;
     }
+    c->n_stale_rows += sc.stale.load();
     return 0;
 }
 
@@ -734,8 +838,10 @@ extern "C" int spl_gpu_dense_fill_synthetic(spl_gpu_ctx *c, uint64_t seed_corpus
         int rc = dev_alloc(c, &c->d_synth_scale, c->n, false);
         if (rc) return rc;
     }
+    if (order_before_update(c)) return -1;
     CUDA_TRY(launch_synth(c->m, c->n, c->slot_begin, seed_corpus, seed_bloom, c->d_synth_scale, c->sm_count, c->stream));
     c->launches += 2;
+    if (order_after_update(c)) return -1;
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     ++c->generation;
     return 0;
@@ -893,7 +999,9 @@ static int ensure_batch_scratch(spl_gpu_ctx *c, uint32_t k) {
     }
     const uint32_t need = kBatchMaxQ * k;
     if (c->bout_cap < need) {
-        if (c->d_bout) { cudaFree(c->d_bout); cudaFree(c->d_bcount); cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount); }
+        cudaFree(c->d_bout); cudaFree(c->d_bcount); cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount);
+        c->d_bout = nullptr; c->d_bcount = nullptr; c->h_bout = nullptr; c->h_bcount = nullptr;   // a failed re-allocation
+        c->bout_cap = 0;                                                                        // must not leave them dangling
         if ((rc = dev_alloc(c, &c->d_bout, need, false))) return rc;
         if ((rc = dev_alloc(c, &c->d_bcount, 2 * kBatchMaxQ, false))) return rc;
         CUDA_TRY(cudaMallocHost((void **)&c->h_bout, (size_t)need * sizeof(spl_gpu_result)));
@@ -932,7 +1040,7 @@ static int enqueue_batch(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
                          uint32_t out_stride, uint32_t *d_counts, uint32_t **d_overflow, cudaStream_t s) {
     BatchArgs b;
     memset(&b, 0, sizeof b);
-    b.E = c->m.E; b.E16 = c->m.E16; b.norm2 = c->m.norm2; b.bloom = c->m.bloom; b.flags = c->m.flags; b.epoch = c->m.epoch;
+    b.E = c->m.E; b.E16 = c->m.E16; b.norm2 = c->m.norm2; b.err2 = c->m.err2; b.norm2_max = c->m.norm2_max; b.bloom = c->m.bloom; b.flags = c->m.flags; b.epoch = c->m.epoch;
     b.n = (uint32_t)c->n; b.dim = c->dim; b.nq = nq; b.order = p->order; b.mask = p->bloom_mask;
     b.min_sim = p->min_similarity; b.max_dist = p->max_distance;
     b.exclude = kIdxSentinel;
@@ -946,19 +1054,13 @@ static int enqueue_batch(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
     return 0;
 }
 
-extern "C" int spl_gpu_search_device(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q,
-                                     spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, void *stream) {
-    int rc = check_params(c, p);
-    if (rc) return rc;
-    if (!d_q || !d_out || !d_counts) return fail(-2, EINVAL, "null device buffer");
-    if (p->k == 0 || p->k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "device search needs k in 1..%u", SPL_GPU_KMAX_FUSED);
-    if (out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
-    cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
-    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+// body of spl_gpu_search_device; c->mu held, stream order already established by the caller
+static int search_device_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q, spl_gpu_result *d_out,
+                                uint32_t out_stride, uint32_t *d_counts, cudaStream_t s) {
+    int rc;
     if (p->mode == SPL_MODE_EXACT) {
-        // no host round trip is possible here, so take the widest candidate margin at once; a query whose
-        // selection still cannot be proven reports 0 hits (the host-buffer call falls back to a full exact pass)
+        // no host round trip is possible here, so take the widest candidate margin at once; a query whose selection
+        // still cannot be proven reports SPL_GPU_COUNT_UNANSWERED (the host-buffer call falls back to a full exact pass)
         if (p->k > kExactMaxK) return fail(-2, EINVAL, "device-buffer exact search needs k <= %u", kExactMaxK);
         if (p->nq > c->q_cap) return fail(-2, EINVAL, "device-buffer exact search takes at most %u queries per call", c->q_cap);
         if ((rc = ensure_exact_scratch(c))) return rc;
@@ -969,10 +1071,29 @@ extern "C" int spl_gpu_search_device(spl_gpu_ctx *c, const spl_gpu_search_params
         if (p->nq > kBatchMaxQ) return fail(-2, EINVAL, "device-buffer batched search takes at most %u queries per call", kBatchMaxQ);
         if ((rc = ensure_batch_scratch(c, p->k))) return rc;
         uint32_t *ovf = nullptr;
-        // a query whose candidate list overflowed reports count 0 here; the host-buffer call re-runs it exactly
+        // a query whose candidate list overflowed, or whose selection the bf16 scores cannot prove, reports
+        // SPL_GPU_COUNT_UNANSWERED here; the host-buffer call re-runs it on the fp32 scan
+        c->n_batch_queries += p->nq;
         return enqueue_batch(c, p, d_q, p->nq, d_out, out_stride, d_counts, &ovf, s);
     }
     return enqueue_fused(c, p, d_q, d_out, out_stride, d_counts, s);
+}
+
+extern "C" int spl_gpu_search_device(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *d_q,
+                                     spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_counts, void *stream) {
+    int rc = check_params(c, p);
+    if (rc) return rc;
+    if (!d_q || !d_out || !d_counts) return fail(-2, EINVAL, "null device buffer");
+    if (p->k == 0 || p->k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "device search needs k in 1..%u", SPL_GPU_KMAX_FUSED);
+    if (out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    if ((rc = order_before_search(c, s))) return rc;
+    rc = search_device_locked(c, p, d_q, d_out, out_stride, d_counts, s);
+    if (rc) c->counters_dirty = true;   // a partly enqueued search may leave the work / ticket counters non-zero
+    const int rc2 = order_after_search(c, s);   // also after a failure: whatever was enqueued still reads the mirror
+    return rc ? rc : rc2;
 }
 
 static int ensure_sort_scratch(spl_gpu_ctx *c, uint32_t out_cap) {
@@ -995,7 +1116,7 @@ static int ensure_sort_scratch(spl_gpu_ctx *c, uint32_t out_cap) {
 // one query, every survivor scored and sorted on the device (the reference's default when --limit is absent);
 // `exact` selects the sequential-order scorer.  Caller holds c->mu.
 static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q_host, bool exact,
-                           spl_gpu_result *out, uint32_t out_stride, uint32_t *count) {
+                           spl_gpu_result *out, uint32_t out_stride, uint32_t *count, uint32_t qi) {
     const uint32_t want = p->k == 0 ? out_stride : p->k;
     const uint32_t cap = want < c->n ? want : (uint32_t)c->n;
     int rc;
@@ -1020,9 +1141,12 @@ static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const
     const uint32_t ncopy = total < cap ? total : cap;
     CUDA_TRY(cudaMemcpy(out, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost));
     *count = p->k == 0 ? total : ncopy;
-    c->h_total[0] = total;  // the sorted pass counts every survivor
+    c->h_total[qi] = total;  // the sorted pass counts every survivor
     return 0;
 }
+
+static int search_host_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
+                              uint32_t out_stride, uint32_t *counts);
 
 extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
                               uint32_t out_stride, uint32_t *counts) {
@@ -1033,11 +1157,29 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
     if (p->k == 0 && out_stride == 0) return fail(-2, EINVAL, "out_stride must be > 0");
     cudaSetDevice(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
+    if ((rc = order_before_search(c, c->stream))) return rc;
+    rc = search_host_locked(c, p, q, out, out_stride, counts);
+    if (rc) {
+        c->counters_dirty = true;
+        order_after_search(c, c->stream);
+        return rc;
+    }
+    // every path above ends with a cudaStreamSynchronize(c->stream): nothing of this search (nor of a caller-stream
+    // search it waited for) is still in flight, so later updates and searches need not wait on it
+    c->search_recorded = false;
+    return 0;
+}
+
+static int search_host_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
+                              uint32_t out_stride, uint32_t *counts) {
+    int rc;
     const size_t qbytes = (size_t)c->dim * sizeof(float);
     const bool fused = p->k >= 1 && p->k <= SPL_GPU_KMAX_FUSED;
+    c->totals_valid = !wants_batch(c, p);
     if (wants_batch(c, p)) {
         if ((rc = check_batch(c, p))) return rc;
         if ((rc = ensure_batch_scratch(c, p->k))) return rc;
+        c->n_batch_queries += p->nq;
         for (uint32_t q0 = 0; q0 < p->nq; q0 += kBatchMaxQ) {
             const uint32_t nq = (p->nq - q0 < kBatchMaxQ) ? p->nq - q0 : kBatchMaxQ;
             CUDA_TRY(cudaMemcpyAsync(c->d_qbatch, q + (size_t)q0 * c->dim, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
@@ -1055,9 +1197,12 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
                 c->last_scan_ms = ms;
             }
             for (uint32_t i = 0; i < nq; i++) {
-                if (c->h_bcount[kBatchMaxQ + i]) {
-                    // candidate list overflowed (threshold from the sample was too loose for this query):
+                c->n_batch_extra += c->h_bcount[kBatchMaxQ + i] >> 1;
+                if (c->h_bcount[kBatchMaxQ + i] & 1u) {
+                    // candidate list overflowed (threshold from the sample was too loose for this query) or the bf16
+                    // scores could not prove the selection (a crowd of near-ties inside the bf16 error bound):
                     // answer it with the fp32 single-query scan instead -- still on the GPU, never on the CPU
+                    c->n_batch_unproven++;
                     spl_gpu_search_params one = *p;
                     one.nq = 1; one.mode = SPL_MODE_FAST;
                     memcpy(c->h_q, q + (size_t)(q0 + i) * c->dim, qbytes);
@@ -1116,15 +1261,18 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
                         memcpy(out + (size_t)(q0 + i) * out_stride, c->h_bounce, (size_t)c->h_bounce_count * sizeof(spl_gpu_result));
                     }
                 }
-                if (!ok && (rc = search_one_full(c, p, q + (size_t)(q0 + i) * c->dim, true, out + (size_t)(q0 + i) * out_stride,
-                                                 out_stride, &counts[q0 + i]))) return rc;
+                if (!ok) {
+                    c->n_exact_unproven++;
+                    if ((rc = search_one_full(c, p, q + (size_t)(q0 + i) * c->dim, true, out + (size_t)(q0 + i) * out_stride,
+                                              out_stride, &counts[q0 + i], q0 + i))) return rc;
+                }
             }
         }
         return 0;
     }
     if (exact) {  // k == 0 (everything, sorted) or k > kExactMaxK: exact score of every row + device-wide sort
         for (uint32_t qi = 0; qi < p->nq; qi++)
-            if ((rc = search_one_full(c, p, q + (size_t)qi * c->dim, true, out + (size_t)qi * out_stride, out_stride, &counts[qi]))) return rc;
+            if ((rc = search_one_full(c, p, q + (size_t)qi * c->dim, true, out + (size_t)qi * out_stride, out_stride, &counts[qi], qi))) return rc;
         return 0;
     }
     if (fused) {
@@ -1156,7 +1304,7 @@ extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
     uint32_t mode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
     if (mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "mode %u is not available for k = %u", mode, p->k);
     for (uint32_t qi = 0; qi < p->nq; qi++)
-        if ((rc = search_one_full(c, p, q + (size_t)qi * c->dim, false, out + (size_t)qi * out_stride, out_stride, &counts[qi]))) return rc;
+        if ((rc = search_one_full(c, p, q + (size_t)qi * c->dim, false, out + (size_t)qi * out_stride, out_stride, &counts[qi], qi))) return rc;
     return 0;
 }
 

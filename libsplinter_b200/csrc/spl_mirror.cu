@@ -10,6 +10,7 @@
 //   epoch  u64  [n]        splinter_slot::epoch at the time the row was copied
 //   E16    bf16 [n][dim]   optional shadow for the tcgen05 batched path
 //   norm2  fp32 [n]        |bf16(e)|^2 for that path
+//   err2   fp32 [n]        |e - bf16(e)|^2: how far rounding moved the row (selection proof of that path)
 #include "spl_mirror.cuh"
 
 #include <cuda_bf16.h>
@@ -27,7 +28,7 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(MirrorPtrs m, const f
         const StagedMeta mt = meta[r];
         const float4 *src = reinterpret_cast<const float4 *>(rows + (size_t)r * m.dim);
         float4 *dst = reinterpret_cast<float4 *>(m.E + (size_t)mt.idx * m.dim);
-        float n2 = 0.f;
+        float n2 = 0.f, er2 = 0.f;
         for (uint32_t c = lane; c < nv; c += 32) {
             const float4 v = src[c];
             dst[c] = v;
@@ -39,17 +40,26 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(MirrorPtrs m, const f
                 *reinterpret_cast<uint2 *>(m.E16 + e16_offset(mt.idx, c * 4, m.dim)) = packed;
                 const float2 a = __bfloat1622float2(lo), b = __bfloat1622float2(hi);
                 n2 += a.x * a.x + a.y * a.y + b.x * b.x + b.y * b.y;
+                const float ex = v.x - a.x, ey = v.y - a.y, ez = v.z - b.x, ew = v.w - b.y;
+                er2 += ex * ex + ey * ey + ez * ez + ew * ew;
             }
         }
         if (m.E16) {
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, off);
+            for (int off = 16; off > 0; off >>= 1) {
+                n2 += __shfl_xor_sync(0xffffffffu, n2, off);
+                er2 += __shfl_xor_sync(0xffffffffu, er2, off);
+            }
         }
         if (lane == 0) {
             m.bloom[mt.idx] = mt.bloom;
             m.epoch[mt.idx] = mt.epoch;
             m.flags[mt.idx] = (uint8_t)mt.flags;
-            if (m.E16) m.norm2[mt.idx] = n2;
+            if (m.E16) {
+                m.norm2[mt.idx] = n2;
+                m.err2[mt.idx] = er2 * 1.0001f;   // rounded up a little: it is used as a bound
+                if (__float_as_uint(n2) > *m.norm2_max) atomicMax(m.norm2_max, __float_as_uint(n2));  // n2 >= 0: bits order like values
+            }
         }
     }
 }
@@ -141,7 +151,7 @@ __global__ void __launch_bounds__(256) synth_fill_kernel(MirrorPtrs m, uint64_t 
     for (uint64_t r = w; r < n; r += nw) {
         const float sc = scale[r];
         const uint64_t hr = mix64(seed_c ^ ((row0 + r) * 0x9E3779B97F4A7C15ull));
-        float n2 = 0.f;
+        float n2 = 0.f, er2 = 0.f;
         for (uint32_t d = lane; d < m.dim; d += 32) {
             const float v = sc != 0.f ? __fmul_rn(synth_raw(hr, d), sc) : 0.f;
             m.E[(size_t)r * m.dim + d] = v;
@@ -150,12 +160,20 @@ __global__ void __launch_bounds__(256) synth_fill_kernel(MirrorPtrs m, uint64_t 
                 m.E16[e16_offset(r, d, m.dim)] = hb;
                 const float fb = __bfloat162float(hb);
                 n2 += fb * fb;
+                er2 += (v - fb) * (v - fb);
             }
         }
         if (m.E16) {
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, off);
-            if (lane == 0) m.norm2[r] = n2;
+            for (int off = 16; off > 0; off >>= 1) {
+                n2 += __shfl_xor_sync(0xffffffffu, n2, off);
+                er2 += __shfl_xor_sync(0xffffffffu, er2, off);
+            }
+            if (lane == 0) {
+                m.norm2[r] = n2;
+                m.err2[r] = er2 * 1.0001f;
+                if (__float_as_uint(n2) > *m.norm2_max) atomicMax(m.norm2_max, __float_as_uint(n2));
+            }
         }
     }
 }

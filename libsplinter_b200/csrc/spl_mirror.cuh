@@ -25,7 +25,9 @@ struct MirrorPtrs {
     uint8_t *flags;
     uint64_t *epoch;
     __nv_bfloat16 *E16;  // nullable; tiled layout, see e16_offset()
-    float *norm2;        // nullable
+    float *norm2;        // nullable: |bf16(e)|^2
+    float *err2;         // nullable: |e - bf16(e)|^2, what rounding the row to bf16 moved it by (selection proof, spl_batch.cu)
+    uint32_t *norm2_max; // nullable: float bits of max norm2 ever written (only grows: an upper bound)
     uint32_t dim;
 };
 

@@ -102,7 +102,13 @@ extern "C" int spl_gpu_scan_noalloc(const float *d_E, const uint64_t *d_bloom, c
                     "(use spl_gpu_search for larger k)", p->k, kNoAllocMaxK, kNoAllocMaxK);
     if (out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
     if (p->nq == 0 || p->nq > 4096) return fail(-2, EINVAL, "nq must be in 1..4096");
-    if (n_rows == 0 || n_rows > 0xFFFFFFF0ull) return fail(-2, EINVAL, "n_rows must be in 1..2^32-16");
+    // the kernel counts 32-row groups in 32 bits: (n + 31) must not wrap
+    if (n_rows == 0 || n_rows > 0xFFFFFFE0ull) return fail(-2, EINVAL, "n_rows must be in 1..2^32-32");
+    // a misaligned arena sub-allocation would otherwise surface as a sticky device fault: rows travel as 16-byte
+    // bulk copies, the query is read as float4, records are written as 32-byte structs
+    if (((uintptr_t)d_E | (uintptr_t)d_q) % 16 || ((uintptr_t)d_out | (uintptr_t)d_bloom | (uintptr_t)d_epoch) % 8 ||
+        (uintptr_t)d_counts % 4)
+        return fail(-2, EINVAL, "misaligned device pointer: E and q need 16-byte alignment, out / bloom / epoch 8, counts 4");
     if (p->order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order %u", p->order);
     if (p->mode != SPL_MODE_AUTO && p->mode != SPL_MODE_FAST) return fail(-1, ENOSYS, "only SPL_MODE_FAST runs without allocation");
     if (!scan_tma_supported(p->dim, p->k))

@@ -290,6 +290,18 @@ merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32
     const uint32_t q = blockIdx.x;
     out += (size_t)q * out_stride;
     out_count += q;
+    // a shard that could not answer this query (SPL_GPU_COUNT_UNANSWERED) makes the merged answer unknowable:
+    // hand the marker on instead of merging the shards that did answer into a wrong top-k
+    __shared__ uint32_t s_unanswered;
+    if (threadIdx.x == 0) s_unanswered = 0;
+    __syncthreads();
+    for (uint32_t l = threadIdx.x; l < nlists; l += blockDim.x)
+        if (counts[(size_t)l * nq + q] == SPL_GPU_COUNT_UNANSWERED) s_unanswered = 1;
+    __syncthreads();
+    if (s_unanswered) {
+        if (threadIdx.x == 0) *out_count = SPL_GPU_COUNT_UNANSWERED;
+        return;
+    }
     for (uint32_t p = threadIdx.x; p < entries; p += blockDim.x) {
         const uint32_t l = p / stride, i = p - l * stride;
         uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;

@@ -13,8 +13,16 @@
  *
  *   ref_writer <store> <key_lo> <key_hi> <seed> <duration_ms> [mix: e r l u in %]
  * Keys are "doc%08d".  Prints "<ops> <set_embedding> <retrain> <label> <unset_set> <eagain>".
+ *
+ * With REF_WRITER_UNIT=1 in the environment every vector is instead a UNIT vector
+ * cos(phi) u + sin(phi) w (u, w fixed orthonormal, phi from the version), so that for a unit
+ * query any search hit must satisfy distance^2 = 2 - 2 similarity (or be the zero row a
+ * retrain / fresh set leaves: similarity 0, distance 1).  A row stitched together from two
+ * versions has a different norm and breaks that identity: the check works on SCORES alone,
+ * which is all a search returns.
  */
 #include <errno.h>
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -50,6 +58,23 @@ int main(int argc, char **argv) {
     if (splinter_open(argv[1]) != 0) { perror("splinter_open"); return 1; }
 
     float vec[SPLINTER_EMBED_DIM];
+    const char *unit_env = getenv("REF_WRITER_UNIT");
+    const int unit = unit_env && unit_env[0] == '1';
+    static double U[SPLINTER_EMBED_DIM], W[SPLINTER_EMBED_DIM];
+    if (unit) {   /* fixed orthonormal pair, the same in every writer process */
+        uint64_t keep = rng_state;
+        rng_state = 777;
+        double uu = 0, uw = 0, ww = 0;
+        for (int d = 0; d < SPLINTER_EMBED_DIM; d++) {
+            U[d] = (double)(rng() >> 11) / 9007199254740992.0 - 0.5;
+            W[d] = (double)(rng() >> 11) / 9007199254740992.0 - 0.5;
+            uu += U[d] * U[d];
+        }
+        for (int d = 0; d < SPLINTER_EMBED_DIM; d++) { U[d] /= sqrt(uu); uw += U[d] * W[d]; }
+        for (int d = 0; d < SPLINTER_EMBED_DIM; d++) { W[d] -= uw * U[d]; ww += W[d] * W[d]; }
+        for (int d = 0; d < SPLINTER_EMBED_DIM; d++) W[d] /= sqrt(ww);
+        rng_state = keep;
+    }
     unsigned long ops = 0, ne = 0, nr = 0, nl = 0, nu = 0, eagain = 0;
     uint32_t version = 1;
     double t_end = now_ms() + dur;
@@ -62,8 +87,14 @@ int main(int argc, char **argv) {
             int rc = 0;
             if (dice < pe) {
                 version++;
-                vec[0] = (float)k; vec[1] = (float)version;
-                for (int d = 2; d < SPLINTER_EMBED_DIM; d++) vec[d] = (float)version + (float)d / 1024.0f;
+                if (unit) {
+                    const double phi = 0.61803398875 * (double)version + 0.001 * (double)k;
+                    const double c = cos(phi), sn = sin(phi);
+                    for (int d = 0; d < SPLINTER_EMBED_DIM; d++) vec[d] = (float)(c * U[d] + sn * W[d]);
+                } else {
+                    vec[0] = (float)k; vec[1] = (float)version;
+                    for (int d = 2; d < SPLINTER_EMBED_DIM; d++) vec[d] = (float)version + (float)d / 1024.0f;
+                }
                 rc = splinter_set_embedding(key, vec); ne++;
             } else if (dice < pe + pr) {
                 rc = splinter_retrain_slot(key); nr++;

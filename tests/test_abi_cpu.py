@@ -31,7 +31,8 @@ def test_struct_layouts_match_the_header():
     assert C.sizeof(sg.SearchParams) == 48
     assert C.sizeof(sg.binding.Opts) == 24
     assert sg.RESULT_DTYPE.itemsize == 32
-    assert C.sizeof(sg.SyncStats) == 80
+    assert C.sizeof(sg.SyncStats) == 96
+    assert C.sizeof(sg.Counters) == 48
     assert C.sizeof(sg.Info) == 64
 
 

@@ -154,3 +154,61 @@ def test_fewer_candidates_than_k():
                 assert set(out[i][:counts[i]]["slot_idx"].tolist()) == set(ref[i][:rc[i]]["idx"].tolist())
     finally:
         m.close()
+
+
+def _near_duplicate_corpus(n, dim, ndup, noise, seed):
+    """n random unit rows, ndup of them replaced by near-copies of one base row: base + noise * |base| * g / sqrt(dim).
+    The realistic adversary of an embedding store (re-ingested or lightly edited documents): bf16 cannot tell them apart."""
+    rng = np.random.default_rng(seed)
+    E = rng.standard_normal((n, dim)).astype(np.float32)
+    E /= np.linalg.norm(E, axis=1, keepdims=True)
+    base = E[0].copy()
+    where = rng.choice(np.arange(1, n), ndup, replace=False)
+    E[where] = base[None, :] + (noise / np.sqrt(dim)) * rng.standard_normal((ndup, dim)).astype(np.float32)
+    bloom = rng.integers(0, 4, n).astype(np.uint64)
+    q = np.concatenate([base[None, :] + 0.2 / np.sqrt(dim) * rng.standard_normal((5, dim)),   # land inside the crowd
+                        rng.standard_normal((3, dim)) / np.sqrt(dim)]).astype(np.float32)     # far from it
+    return np.ascontiguousarray(E), bloom, q
+
+
+@pytest.mark.parametrize("dim", [768, 1024])
+@pytest.mark.parametrize("ndup,noise", [(3000, 1e-2), (10_000, 1e-3), (3000, 1e-4), (200, 1e-2)])
+def test_near_duplicates_do_not_fool_the_bf16_selection(dim, ndup, noise):
+    """The bf16 pass only PROPOSES rows; the selection proof in select_rerank_kernel decides whether the proposal can
+    be trusted.  With thousands of rows packed inside one bf16 error bound of the k-th score it cannot, and the query
+    goes to the fp32 scan; with a couple of hundred the kernel re-scores them all itself.  Either way the answer is
+    the reference's: same indices (where fp32 itself separates the rows), both orders, with and without a mask."""
+    n, k = 60_000, 32
+    E, bloom, q = _near_duplicate_corpus(n, dim, ndup, noise, seed=ndup + dim)
+    flags = np.full(n, 7, np.uint8)
+    with sg.Mirror.open_dense(n, dim, flags=sg.OPT_BF16_MIRROR) as m:
+        m.dense_upload(0, E, bloom, flags)
+        for order in (sg.ORDER_COSINE, sg.ORDER_L2):
+            for mask in (0, 0x1):
+                c0 = m.counters()
+                bad = _check(m, E, bloom, flags, q, k, order=order, bloom_mask=mask)
+                c1 = m.counters()
+                if noise >= 1e-3:
+                    assert bad == 0, f"{bad} queries differ in their indices (order {order}, mask {mask})"
+                if ndup >= 3000:    # more near-ties than the kernel may re-score: those queries took the fp32 scan
+                    assert c1.batch_unproven > c0.batch_unproven
+                else:               # a small crowd is re-scored inside the kernel, nothing falls back
+                    assert c1.batch_unproven == c0.batch_unproven
+                    assert c1.batch_rescored_extra > c0.batch_rescored_extra
+
+
+def test_random_corpus_needs_no_fallback():
+    """On the synthetic corpus of the benchmark the proof goes through for every query (a few re-score a handful of
+    extra rows): the slow path is for adversarial data, not the common case."""
+    n, dim, nq, k = 200_000, 1024, 128, 32
+    m, E, bloom, flags = _mirror(n, dim)
+    q = support.synth_queries(4321, nq, dim)
+    try:
+        for order in (sg.ORDER_L2, sg.ORDER_COSINE):
+            c0 = m.counters()
+            assert _check(m, E, bloom, flags, q, k, order=order) == 0
+            c1 = m.counters()
+            assert c1.batch_queries - c0.batch_queries == nq
+            assert c1.batch_unproven == c0.batch_unproven
+    finally:
+        m.close()

@@ -33,10 +33,13 @@ def _call(lib, cols, n, row0, p, d_q, d_out, stride, d_cnt, stream=0):
                                     C.c_void_p(stream))
 
 
-def test_noalloc_scan_matches_the_allocating_entry_point_twice_in_a_row():
+# k = 10 ends in the register / shuffle epilogue; k = 64 in the block-wide sort with the anchor selection and uses the
+# whole fixed scratch (64 candidates per CTA); 20 rows leave all but one CTA without any work
+@pytest.mark.parametrize("n,k", [(40_000, 10), (40_000, 64), (20, 10)])
+def test_noalloc_scan_matches_the_allocating_entry_point_twice_in_a_row(n, k):
     import torch
     lib = sg.load()
-    n, dim, k, row0 = 40_000, 768, 10, 1000
+    dim, row0 = 768, 1000
     E, bloom, flags = support.synth_dense(1234, 99, row0, n, dim)
     epoch = np.where(flags != 0, 4, 0).astype(np.uint64)
     q = support.synth_queries(4321, 3, dim)
@@ -103,3 +106,9 @@ def test_noalloc_scan_refuses_what_its_fixed_scratch_cannot_hold():
         rc = _call(lib, cols, n, 0, p, d_q, d_out, 128, d_cnt)
         assert rc == -2
         assert msg in lib.spl_gpu_last_error().decode()
+    # a sub-allocation of the caller's arena that is not aligned for the row copies is refused, not faulted on
+    p = sg.SearchParams(C.sizeof(sg.SearchParams), 1, dim, 10, sg.ORDER_COSINE, sg.MODE_AUTO, 0, 0.0, 0.0, sg.NO_SLOT, 0)
+    skewed = (cols[0].view(-1)[1:1 + (n - 1) * dim].view(n - 1, dim),) + cols[1:]
+    rc = _call(lib, skewed, n - 1, 0, p, d_q, d_out, 128, d_cnt)
+    assert rc == -2 and "misaligned" in lib.spl_gpu_last_error().decode()
+    torch.cuda.synchronize()
