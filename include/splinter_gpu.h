@@ -214,6 +214,12 @@ int spl_gpu_read_mirror(spl_gpu_ctx *ctx, uint64_t first_slot, uint64_t n, float
 int spl_gpu_slot_meta(const spl_gpu_ctx *ctx, uint32_t slot_idx, char key_out[64], uint32_t *val_len,
                       uint8_t *type_flag);
 
+/* Find the slot a key lives in: FNV-1a of the key, linear probe from hash % slots comparing the hash and then
+ * the key -- the lookup every keyed call of the reference starts with (splinter.c:67-81, 535-539).  The search
+ * command needs it once per query, for the scratch key it must leave out of the results (_search.c:367).
+ * Store-backed contexts only; reads the live store.  0 = found (*slot_idx set), -1 / ENOENT = no such key. */
+int spl_gpu_find_key(const spl_gpu_ctx *ctx, const char *key, uint32_t *slot_idx);
+
 /* ---- search ------------------------------------------------------------------------- */
 
 /* Host-buffer search (the reference-facing call).  q = nq x dim fp32.  out = nq x out_stride

@@ -21,7 +21,7 @@ ABI_SYMBOLS = [
     "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_wait", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
     "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device", "spl_gpu_merge_topk_batch_device",
     "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
-    "spl_gpu_get_counters",
+    "spl_gpu_get_counters", "spl_gpu_find_key",
 ]
 
 ORDER_COSINE, ORDER_L2 = 0, 1
@@ -118,6 +118,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_scan_noalloc.argtypes = [vp, vp, vp, vp, u64, u64, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_slot_meta.restype = C.c_int
     lib.spl_gpu_slot_meta.argtypes = [vp, u32, C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint8)]
+    lib.spl_gpu_find_key.restype = C.c_int
+    lib.spl_gpu_find_key.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint32)]
     lib.spl_gpu_last_totals.restype = C.c_int
     lib.spl_gpu_last_totals.argtypes = [vp, vp, u32]
     lib.spl_gpu_launch_count.restype = u64
@@ -272,6 +274,12 @@ class Mirror:
         self._check(self._lib.spl_gpu_merge_topk_batch_device(self._h, C.c_void_p(d_lists), C.c_void_p(d_counts), nlists, nq,
                                                               stride, order, k, C.c_void_p(d_out), out_stride,
                                                               C.c_void_p(d_out_counts), C.c_void_p(stream)))
+
+    def find_key(self, key: str):
+        """slot index of `key` in the live store, or None"""
+        idx = C.c_uint32(0)
+        rc = self._lib.spl_gpu_find_key(self._h, key.encode(), C.byref(idx))
+        return int(idx.value) if rc == 0 else None
 
     def last_totals(self, nq=1):
         t = np.zeros(nq, np.uint32)

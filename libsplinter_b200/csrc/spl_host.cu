@@ -47,6 +47,7 @@ constexpr size_t S_HASH = 0, S_EPOCH = 8, S_VAL_LEN = 20, S_BLOOM = 56, S_KEY = 
 }  // namespace layout
 
 static thread_local char g_err[512] = "";
+static inline uint64_t ld_acq64(const uint8_t *p);
 
 static int fail(int rc, int err, const char *fmt, ...) {
     va_list ap;
@@ -416,6 +417,23 @@ extern "C" int spl_gpu_slot_meta(const spl_gpu_ctx *c, uint32_t slot_idx, char k
     if (val_len) *val_len = __atomic_load_n(reinterpret_cast<const uint32_t *>(sl + layout::S_VAL_LEN), __ATOMIC_ACQUIRE);
     if (type_flag) *type_flag = sl[24];
     return 0;
+}
+
+extern "C" int spl_gpu_find_key(const spl_gpu_ctx *c, const char *key, uint32_t *slot_idx) {
+    if (!c || !key || !slot_idx) return fail(-2, EINVAL, "null argument");
+    if (c->dense || !c->base) return fail(-2, EINVAL, "dense contexts have no keys");
+    uint64_t h = 14695981039346656037ull;                                   // FNV-1a, splinter.c:67-71
+    for (const unsigned char *s = (const unsigned char *)key; *s; ++s) h = (h ^ *s) * 1099511628211ull;
+    const uint64_t slots = c->total_slots, first = h % slots;
+    for (uint64_t i = 0; i < slots; i++) {                                   // linear probe, splinter.c:535-539
+        const uint64_t idx = (first + i) % slots;
+        const uint8_t *sl = c->base + layout::kHeaderSize + idx * c->slot_size;
+        if (ld_acq64(sl + layout::S_HASH) == h && strncmp((const char *)sl + layout::S_KEY, key, 64) == 0) {
+            *slot_idx = (uint32_t)idx;
+            return 0;
+        }
+    }
+    return fail(-1, ENOENT, "no slot holds key '%.64s'", key);
 }
 
 extern "C" int spl_gpu_last_totals(const spl_gpu_ctx *c, uint32_t *totals, uint32_t nq) {
