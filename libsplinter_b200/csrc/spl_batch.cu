@@ -295,6 +295,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
             const float thr = (a.pass == 2 && qvalid) ? a.thr[q] : -INFINITY;
             const uint32_t thr_row = (a.pass == 2 && qvalid) ? a.thr_row[q] : 0u;
             uint32_t acc = 0, aph = 0;
+            // selection proof (select_rerank_kernel): the best ordering value among the rows this thread leaves OUT of
+            // its query's candidate list, and whether rows tying with the bound were cut off by their row index
+            float out_min = INFINITY;
+            uint32_t out_tie = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 const uint32_t row0 = (a.tile_first + j * a.tile_stride) * BN;
                 bar_wait(CFULL(acc), aph);
@@ -337,8 +341,16 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                                     a.cand_t[(size_t)q * a.cand_cap + pos] = t;
                                     a.cand_idx[(size_t)q * a.cand_cap + pos] = row0 + c0 + i;
                                 }
+                            } else if (t < INFINITY && t == thr) {
+                                // ties with the bound that the row index cut off: rows whose coefficient is 0 score exactly
+                                // (zero vector / no embedding), the others are ordinary rows that happen to tie in bf16
+                                out_tie |= pa[c0 + i] == 0.f ? 1u : 2u;
+                            } else {
+                                out_min = fminf(out_min, t);
                             }
                         }
+                    } else {
+                        out_min = fminf(out_min, cmin);   // the whole chunk stays out: remember the best value left out
                     }
                 }
                 tc_fence_before();
@@ -352,6 +364,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                     a.tile_min_row[(size_t)j * a.nq_pad + q] = imin;
                 }
                 if (++acc == kAcc) { acc = 0; aph ^= 1u; }
+            }
+            if (a.pass == 2 && qvalid) {
+                if (out_min < INFINITY) atomicMin(&a.out_min[q], f2ord(out_min));
+                if (out_tie) atomicOr(&a.out_tie[q], out_tie);
             }
         }
     }
@@ -519,19 +535,37 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
     if (a.max_dist > 0.f) Dk = fminf(Dk, a.max_dist);
     const float DkUp = Dk * (1.0f + kScanTol);
     const float thq = qn > 0.f ? asin_upper(dqn / qn) : 3.2f;
+    // Rows whose score is known without reading them: a zero vector scores (0, |q|) -- with exactly the bits the
+    // re-score produces, ma above is the same sum in the same order -- and a row without a consistent embedding copy
+    // (0, FLT_MAX), _search.c:388-391.  They compare EXACTLY, ties by row index like everywhere else; that matters:
+    // the synthetic corpus holds thousands of never-embedded zero rows that tie at distance |q|.
+    const uint64_t key_zero = make_key(a.order, 0.f, __fsqrt_rn(ma)), key_noemb = make_key(a.order, 0.f, FLT_MAX);
+    const uint64_t xkey = have_k ? rk[k - 1] : kKeySentinel;
+    const uint32_t xidx = have_k ? ri[k - 1] : kIdxSentinel;
+    const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
+    auto exact_excluded = [&](uint64_t key, uint32_t row, bool emb) {
+        if (thresholds) {   // rows failing the threshold are never results
+            float sim, dist;
+            split_key(a.order, key, sim, dist);
+            if (!emb || (a.min_sim > 0.f && sim < a.min_sim) || (a.max_dist > 0.f && dist > a.max_dist)) return true;
+        }
+        return have_k && !better(key, row, xkey, xidx);
+    };
     for (uint32_t c = m + threadIdx.x; c < total; c += blockDim.x) {
         const uint32_t row = idx[c];
         const float t = ord2f((uint32_t)keys[c]);
         bool excluded;
-        if (!(a.flags[row] & SPL_ROW_EMB)) {       // scores are exactly (0, FLT_MAX): _search.c:388-391
-            excluded = cosine ? (0.f < S) : (FLT_MAX > DkUp);
+        const bool emb = (a.flags[row] & SPL_ROW_EMB) != 0;
+        const float n2 = emb ? a.norm2[row] : 0.f, er2 = emb ? a.err2[row] : 0.f;
+        if (!emb) {
+            excluded = exact_excluded(key_noemb, row, false);
+        } else if (n2 == 0.f && er2 == 0.f) {
+            excluded = exact_excluded(key_zero, row, true);
         } else {
-            const float n2 = a.norm2[row], er2 = a.err2[row];
             const float en16 = sqrtf(n2), de = sqrtf(er2) * 1.000001f;
             if (cosine) {
                 float sim_up;
-                if (n2 == 0.f && er2 == 0.f) sim_up = 0.f;                    // a zero row scores exactly 0
-                else if (!(qn16 > 0.f) || en16 <= 2.f * de) sim_up = INFINITY;  // no usable bound
+                if (!(qn16 > 0.f) || en16 <= 2.f * de) sim_up = INFINITY;  // no usable bound
                 else sim_up = -t / qn16 + thq + asin_upper(de / en16) + kTcAccRel + kScanTol;
                 excluded = sim_up < S;
             } else {
@@ -546,21 +580,32 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
             if (m + pos < kRescoreCap) ri[m + pos] = row;   // (slots >= R are written here for the first time)
         }
     }
-    if (threadIdx.x == 0 && a.thr[q] < INFINITY) {
-        // rows that never entered the list have an ordering value >= thr
-        const float thr = a.thr[q];
-        bool ok;
-        if (cosine) {
-            const float sim_up = qn16 > 0.f ? -thr / qn16 + thq + asin_upper(kBf16Unit) + kTcAccRel + kScanTol : INFINITY;
-            ok = sim_up < S;
-        } else {
+    if (threadIdx.x == 0) {
+        // Rows that never entered the list.  Pass 2 left behind, per query, the best ordering value among the rows it
+        // kept out because they were WORSE than the bound (out_min), and whether rows TYING with the bound were cut off
+        // by their row index (out_tie: bit 0 = rows that score exactly, bit 1 = ordinary rows).
+        auto bound_clears = [&](float t16) {   // can a row whose bf16 ordering value is >= t16 still reach X?
+            if (cosine) {
+                const float sim_up = qn16 > 0.f ? -t16 / qn16 + thq + asin_upper(kBf16Unit) + kTcAccRel + kScanTol : INFINITY;
+                return sim_up < S;
+            }
             // |e16| of an unknown row: at most the shard's maximum, and a row with |e| > Dk + |q| is farther than Dk anyway
             float emax = sqrtf(__uint_as_float(*a.norm2_max));
             if (Dk < INFINITY) emax = fminf(emax, 1.004f * (Dk + qn));
             const float de = kBf16Unit * 1.004f * emax;
             const float delta = 2.f * kTcAccRel * qn16 * emax + 1e-5f * (emax * emax + mq16);
-            const float lo = sqrtf(fmaxf(0.f, thr + mq16 - delta)) * (1.0f - 1e-6f) - (dqn + de) * (1.0f + kScanTol);
-            ok = lo > DkUp;
+            const float lo = sqrtf(fmaxf(0.f, t16 + mq16 - delta)) * (1.0f - 1e-6f) - (dqn + de) * (1.0f + kScanTol);
+            return lo > DkUp;
+        };
+        bool ok = true;
+        const uint32_t omin = a.out_min[q], tie = a.out_tie[q];
+        if (omin != 0xFFFFFFFFu) ok = bound_clears(ord2f(omin));
+        if (ok && (tie & 2u)) ok = bound_clears(a.thr[q]);
+        if (ok && (tie & 1u)) {
+            // exactly-scoring rows tying with the bound, all with a row index beyond thr_row: the best they can be is a
+            // zero row (or, at the far end of the L2 order, a row without embedding) at index thr_row + 1
+            const bool noemb = !cosine && a.thr[q] > 1e38f;
+            ok = exact_excluded(noemb ? key_noemb : key_zero, a.thr_row[q] + 1u, !noemb);
         }
         if (!ok) s_fail = 1;
     }
@@ -684,6 +729,8 @@ size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, Batch
     L->thr_row_off = take((size_t)nq_pad * 4);
     L->cnt_off = take((size_t)nq_pad * 4);
     L->ovf_off = take((size_t)nq_pad * 4);
+    L->out_min_off = take((size_t)nq_pad * 4);
+    L->out_tie_off = take((size_t)nq_pad * 4);
     L->tile_min_off = take((size_t)tiles * nq_pad * 4);
     L->tile_min_row_off = take((size_t)tiles * nq_pad * 4);
     L->cand_t_off = take((size_t)nq_pad * kBatchCandCap * 4);
@@ -704,6 +751,8 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     a.tile_min_row = reinterpret_cast<uint32_t *>(scratch + L.tile_min_row_off);
     a.cand_cnt = reinterpret_cast<uint32_t *>(scratch + L.cnt_off);
     uint32_t *overflow = reinterpret_cast<uint32_t *>(scratch + L.ovf_off);
+    a.out_min = reinterpret_cast<uint32_t *>(scratch + L.out_min_off);
+    a.out_tie = reinterpret_cast<uint32_t *>(scratch + L.out_tie_off);
     a.tile_min = reinterpret_cast<float *>(scratch + L.tile_min_off);
     a.cand_t = reinterpret_cast<float *>(scratch + L.cand_t_off);
     a.cand_idx = reinterpret_cast<uint32_t *>(scratch + L.cand_idx_off);
@@ -723,6 +772,8 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     if ((e = cudaGetLastError())) return e;
     if ((e = cudaMemsetAsync(a.cand_cnt, 0, (size_t)a.nq_pad * 4, s))) return e;
     if ((e = cudaMemsetAsync(overflow, 0, (size_t)a.nq_pad * 4, s))) return e;
+    if ((e = cudaMemsetAsync(a.out_min, 0xFF, (size_t)a.nq_pad * 4, s))) return e;
+    if ((e = cudaMemsetAsync(a.out_tie, 0, (size_t)a.nq_pad * 4, s))) return e;
 
     const uint32_t tiles = (a.n + BN - 1) / BN;
     int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;

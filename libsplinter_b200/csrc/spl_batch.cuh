@@ -35,6 +35,8 @@ struct BatchArgs {
     uint32_t *thr_row;            // [nq_pad]   ... and, for ties on t, on the row index
     float *tile_min;              // [n_tiles][nq_pad]
     uint32_t *tile_min_row;       // [n_tiles][nq_pad]
+    uint32_t *out_min;            // [nq_pad]   f2ord of the best ordering value pass 2 kept OUT of the list as worse than thr
+    uint32_t *out_tie;            // [nq_pad]   bit 0 / 1: exactly-scoring / ordinary rows tying with thr were cut off by row index
     uint32_t *cand_cnt;           // [nq_pad]
     float *cand_t;                // [nq_pad][cand_cap]
     uint32_t *cand_idx;           // [nq_pad][cand_cap]
@@ -42,7 +44,7 @@ struct BatchArgs {
 };
 
 struct BatchScratchLayout {
-    size_t q16_off, thr_off, thr_row_off, cnt_off, ovf_off, tile_min_off, tile_min_row_off, cand_t_off, cand_idx_off;
+    size_t q16_off, thr_off, thr_row_off, cnt_off, ovf_off, out_min_off, out_tie_off, tile_min_off, tile_min_row_off, cand_t_off, cand_idx_off;
     uint32_t nq_pad;
 };
 
