@@ -237,10 +237,6 @@ def run_ours(args):
     q_dev = torch.from_numpy(q_host).to(dev)
     out_dev = torch.zeros((k, 32), dtype=torch.uint8, device=dev)
     cnt_dev = torch.zeros(1, dtype=torch.int32, device=dev)
-    gathered = torch.zeros((world * k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
-    gcnt = torch.zeros(world, dtype=torch.int32, device=dev) if world > 1 else None
-    fin_dev = torch.zeros((k, 32), dtype=torch.uint8, device=dev) if world > 1 else None
-    fcnt_dev = torch.zeros(1, dtype=torch.int32, device=dev) if world > 1 else None
     q_pin = torch.from_numpy(q_host).pin_memory()
     res_pin = torch.zeros((k, 32), dtype=torch.uint8).pin_memory()
     # A dedicated (non-default) stream: the kernels, the NCCL ops and the timing events must all sit on
@@ -249,6 +245,10 @@ def run_ours(args):
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
     assert stream != 0
+    from libsplinter_b200.sharding import ShardedSearcher
+    # N > 1: shard scan -> ONE all-gather of the packed {records, count} block per query -> merge on every rank
+    sharded = ShardedSearcher(m, world, 1, k, sg.ORDER_COSINE, dev, stream) if world > 1 else None
+    fin_dev = sharded.fin if sharded else None
 
     def n_pass_of(mask):
         need = sg.ROW_ENUM if mask else sg.ROW_LIST
@@ -256,13 +256,11 @@ def run_ours(args):
 
     def device_step(i, mask, qsrc=None):
         p = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask)
-        qptr = (qsrc if qsrc is not None else q_dev[i % N_QUERIES]).data_ptr()
-        m.search_device(p, qptr, out_dev.data_ptr(), k, cnt_dev.data_ptr(), stream)
+        qv = qsrc if qsrc is not None else q_dev[i % N_QUERIES]
         if world > 1:
-            dist.all_gather_into_tensor(gathered, out_dev)
-            dist.all_gather_into_tensor(gcnt, cnt_dev)
-            m.merge_topk_device(gathered.data_ptr(), gcnt.data_ptr(), world, k, sg.ORDER_COSINE, k,
-                                fin_dev.data_ptr(), fcnt_dev.data_ptr(), stream)
+            sharded.enqueue(p, qv)      # (fp32 scan: always answers, no re-issue to wait for)
+        else:
+            m.search_device(p, qv.data_ptr(), out_dev.data_ptr(), k, cnt_dev.data_ptr(), stream)
 
     def barrier():
         if world > 1:
@@ -298,7 +296,7 @@ def run_ours(args):
             else:
                 qbuf.copy_(q_pin[i % N_QUERIES], non_blocking=True)
                 device_step(i, mask, qsrc=qbuf)
-                res_pin.copy_(fin_dev, non_blocking=True)
+                res_pin.copy_(fin_dev.view(k, 32), non_blocking=True)
                 torch.cuda.current_stream().synchronize()
         for i in range(warmup):
             one(i)
@@ -383,6 +381,16 @@ def run_ours(args):
 
     # ---- parity gate on the timed configuration (rank-local shard sample vs oracle) ----
     parity = parity_gate(m, sg, support, rows, row0, k, head_mask)
+    if world > 1:   # ... and on the MERGED answer every rank ends up with
+        parity.update(merged_parity_gate(sharded, m, sg, support, torch, dist, q_host, q_dev, k, head_mask, world, rank, dev))
+
+    # ---- same-workload single-GPU anchor for the C4 scaling curve (N = 1 only): the largest shard that fits ----
+    anchor = c4_anchor_leg(sg, support, torch, dev, stream, peak, local_rank) if single and not args.skip_extra else None
+    # ---- C5: mixed workload across all ranks (N = 8 by default; SPL_BENCH_C5_SLOTS forces it at any N > 1) ----
+    c5 = None
+    c5_slots = int(os.environ.get("SPL_BENCH_C5_SLOTS", str(1 << 24) if world == 8 else "0"))
+    if world > 1 and c5_slots and not args.skip_extra:
+        c5 = c5_mixed_leg(sg, support, torch, dist, c5_slots, world, rank, local_rank, dev, tstream)
 
     if rank == 0:
         gbs = job_bytes / ms_step / 1e6
@@ -419,6 +427,10 @@ def run_ours(args):
             line["small_batch_4q"] = small
         if c3:
             line["c3_batched"] = c3
+        if anchor:
+            line["c4_single_gpu_anchor"] = anchor
+        if c5:
+            line["c5_mixed"] = c5
         if single and not args.skip_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(k, head_mask)
         print(json.dumps(line))
@@ -508,6 +520,233 @@ def parity_gate(m, sg, support, rows, row0, k, mask):
         return {"checked_slots": sample, "ok": False, "error": str(e)[:200]}
 
 
+def _oracle_rescore(support, q, global_idx):
+    """(similarity, distance) of the synthetic corpus row `global_idx` against q, by the oracle's scorers"""
+    E, _, flags = support.synth_dense(SEED_CORPUS, SEED_BLOOM, int(global_idx), 1, DIM, threads=1)
+    if not (flags[0] & support.F_EMB):
+        return 0.0, float(np.finfo(np.float32).max)
+    return (float(support.oracle().splo_cosine(support._p(q), support._p(E[0]), DIM)),
+            float(support.oracle().splo_euclid(support._p(q), support._p(E[0]), DIM)))
+
+
+def merged_parity_gate(sharded, m, sg, support, torch, dist, q_host, q_dev, k, mask, world, rank, dev):
+    """One query through scan -> all-gather -> merge, then: every rank re-scores ITS local hits with the oracle (rows
+    regenerated from the counter RNG); rank 0 re-scores the k merged hits, checks their order, and checks that the merged
+    list is exactly the k best of all ranks' local hits under the reference comparator + global slot index."""
+    from libsplinter_b200.binding import packed_block_bytes
+    p = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask)
+    fin, fcnt = sharded.enqueue(p, q_dev[0:1])
+    torch.cuda.synchronize()
+    block, gathered = sharded._buffers(1)[:2]
+    bb = packed_block_bytes(1, k)
+    g = gathered.cpu().numpy().reshape(world, bb)
+    lists = [g[w][:k * 32].view(sg.RESULT_DTYPE) for w in range(world)]
+    counts = [int(g[w][k * 32:k * 32 + 4].view(np.uint32)[0]) for w in range(world)]
+    merged = fin.cpu().numpy().reshape(k * 32).view(sg.RESULT_DTYPE)[:int(fcnt.cpu()[0])]
+    q = q_host[0]
+
+    def rescored_ok(recs):
+        for r in recs:
+            sim, dist_ = _oracle_rescore(support, q, r["slot_idx"])
+            if abs(sim - float(r["similarity"])) > support.TOL_SIM:
+                return False
+            if dist_ < 3e38 and abs(dist_ - float(r["distance"])) > support.TOL_DIST_REL * dist_ + 1e-7:
+                return False
+        return True
+
+    local_ok = rescored_ok(lists[rank][:counts[rank]])
+    t = torch.tensor([1 if local_ok else 0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    out = {"local_hits_rescored_ok_all_ranks": bool(int(t.item()))}
+    if rank == 0:
+        pool = np.concatenate([lists[w][:counts[w]] for w in range(world)])
+        # reference comparator (similarity desc, distance asc) + global slot index asc
+        order = np.lexsort((pool["slot_idx"], pool["distance"], -pool["similarity"].astype(np.float64)))
+        want = pool[order][:k]
+        out["merged_is_topk_of_all_local_hits"] = bool(want.tobytes() == merged.tobytes())
+        out["merged_hits_rescored_ok"] = bool(rescored_ok(merged))
+        out["merged_ok"] = bool(out["merged_is_topk_of_all_local_hits"] and out["merged_hits_rescored_ok"]
+                                and out["local_hits_rescored_ok_all_ranks"] and len(merged) == k)
+        out["merged_from_ranks"] = sorted({int(r["slot_idx"]) * world // C4_ROWS for r in merged})
+    return out
+
+
+def c4_anchor_leg(sg, support, torch, dev, stream, peak, device_index):
+    """The C4 workload (unfiltered cosine top-100) on ONE GPU over the largest power-of-two shard that fits (2^25 rows,
+    103 GB): the like-for-like N = 1 point for the N = 2/4/8 lines, whose headline N = 1 run is C2."""
+    rows, k = 1 << 25, C4_K
+    free, _ = torch.cuda.mem_get_info()
+    while rows * (4 * DIM + 17) * 1.05 > free and rows > (1 << 20):
+        rows >>= 1
+    m = sg.Mirror.open_dense(rows, DIM, device=device_index)
+    try:
+        m.fill_synthetic(SEED_CORPUS, SEED_BLOOM)
+        q = torch.from_numpy(support.synth_queries(SEED_QUERY, 8, DIM)).to(dev)
+        out = torch.zeros((k, 32), dtype=torch.uint8, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+        p = m.params(1, k, mode=sg.MODE_AUTO)
+        for i in range(3):
+            m.search_device(p, q[i].data_ptr(), out.data_ptr(), k, cnt.data_ptr(), stream)
+        torch.cuda.synchronize()
+        steps = 12
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            m.search_device(p, q[i % 8].data_ptr(), out.data_ptr(), k, cnt.data_ptr(), stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        _, bloom_h, flags_h, _ = m.read_mirror(0, rows, want_E=False)
+        b = algorithmic_bytes(rows, int(((flags_h & sg.ROW_LIST) != 0).sum()))
+        return {"workload": f"C4's query (unfiltered cosine top-{k}) over one {rows}-slot shard on one GPU",
+                "slots": rows, "ms_per_step": round(ms, 4), "queries_per_s": round(1e3 / ms, 2),
+                "scanned_GB_per_s": round(b / ms / 1e6, 1), "roofline_frac": round(b / ms / 1e6 / peak, 4),
+                "queries_per_s_scaled_to_2p26": round(1e3 / ms * rows / C4_ROWS, 3)}
+    finally:
+        m.close()
+
+
+def _unit_identity_violations(recs):
+    """hits of unit queries over unit-or-zero rows: distance^2 = 2 - 2 similarity, or (0, 1) for a zero row, or
+    (0, FLT_MAX, has_embedding 0) for a slot whose first copy is still pending"""
+    sim = recs["similarity"].astype(np.float64)
+    dist_ = recs["distance"].astype(np.float64)
+    ok = np.abs(dist_ * dist_ - (2.0 - 2.0 * sim)) <= 2e-4
+    ok |= (sim == 0.0) & (np.abs(dist_ - 1.0) <= 1e-5)
+    ok |= (recs["has_embedding"] == 0) & (sim == 0.0)
+    ok &= recs["epoch"] % 2 == 0
+    return int(np.count_nonzero(~ok))
+
+
+def c5_mixed_leg(sg, support, torch, dist, slots, world, rank, local_rank, dev, tstream):
+    """Config C5: ONE reference-format store in /dev/shm, every rank mirrors its slot range (fp32 + bf16), writer
+    PROCESSES mutate the store through the reference's API (80% set_embedding, 10% retrain_slot, 5% labels, 5% unset+set;
+    splinter_chi_sao.c's disjoint key lanes), every rank keeps syncing its range, and nq = 64 batched cosine top-10
+    searches run across all ranks (tensor-core shard search on a caller stream -> one all-gather -> merge).  Parity is
+    sampled WHILE the writers run -- every vector in the store is a unit vector or zero, so a hit from a torn row breaks
+    distance^2 = 2 - 2 similarity -- and against the CPU oracle over the whole store once they have stopped."""
+    import mmap
+    from libsplinter_b200.sharding import ShardedSearcher, shard_range
+    NQ, K, MAXVAL, SECONDS, PERIOD = 64, 10, 64, 6.0, 0.1
+    avail = 0
+    for ln in open("/proc/meminfo"):
+        if ln.startswith("MemAvailable"):
+            avail = int(ln.split()[1]) * 1024
+    while support.oracle().splo_image_size(slots, MAXVAL, DIM) * 1.3 > avail and slots > (1 << 16):
+        slots >>= 1
+    t = torch.tensor([slots], device=dev, dtype=torch.int64)
+    dist.broadcast(t, 0)
+    slots = int(t.item())
+    size = support.oracle().splo_image_size(slots, MAXVAL, DIM)
+    name = f"/splb200_c5_{os.environ.get('MASTER_PORT', '0')}"
+    path = "/dev/shm" + name
+    out = {"workload": f"C5: {slots} slots x 768-d in one store, concurrent writers + incremental re-upload + batched search",
+           "slots": slots, "store_bytes": int(size), "nq": NQ, "k": K, "gpus": world}
+    img = None
+    if rank == 0:
+        if os.path.exists(path):
+            os.unlink(path)
+        with open(path, "wb") as f:
+            f.truncate(size)
+        fd = os.open(path, os.O_RDWR)
+        mm = mmap.mmap(fd, size)
+        img = np.frombuffer(mm, np.uint8)
+        t0 = time.perf_counter()
+        assert support.oracle().splo_image_init(support._p(img), slots, MAXVAL, DIM) == 0
+        out["keys_placed"] = int(support.image_fill_synthetic(img, slots // 2))
+        out["host_build_s"] = round(time.perf_counter() - t0, 2)
+    dist.barrier()
+    m = None
+    try:
+        lo, cnt = shard_range(slots, world, rank)
+        t0 = time.perf_counter()
+        m = sg.Mirror.attach(name, slot_begin=lo, slot_count=cnt, flags=sg.OPT_BF16_MIRROR, device=local_rank,
+                             sync_threads=max(2, (os.cpu_count() or 8) // world))
+        attach_s = time.perf_counter() - t0
+        dist.barrier()
+        q_host = support.synth_queries(777, NQ, DIM)
+        dq = torch.from_numpy(q_host).to(dev)
+        S = ShardedSearcher(m, world, NQ, K, sg.ORDER_COSINE, dev, tstream.cuda_stream)
+        p = m.params(NQ, K, mode=sg.MODE_BATCH_BF16, order=sg.ORDER_COSINE)
+        for _ in range(3):
+            S.search(p, dq)
+        dist.barrier()
+        syncs, stop = [], threading.Event()
+
+        def syncer():
+            while not stop.is_set():
+                m.wait(100)
+                t0 = time.perf_counter()
+                st = m.sync()
+                dt = time.perf_counter() - t0
+                syncs.append((dt, st.rows_uploaded, st.skipped_busy))
+                if PERIOD > dt:
+                    time.sleep(PERIOD - dt)
+
+        procs = []
+        if rank == 0:
+            writer, nkeys, lanes = str(support.REF_DIR / "ref_writer"), slots // 2, 4
+            procs = [subprocess.Popen([writer, name, str(i * (nkeys // lanes)), str((i + 1) * (nkeys // lanes)), str(77 + i),
+                                       str(int(SECONDS * 1e3))], stdout=subprocess.PIPE, text=True,
+                                      env={**os.environ, "REF_WRITER_UNIT": "1"}) for i in range(lanes)]
+        th = threading.Thread(target=syncer)
+        th.start()
+        flag = torch.ones(1, dtype=torch.int32, device=dev)
+        batches, t_search, live_hits, live_bad, t_begin = 0, 0.0, 0, 0, time.perf_counter()
+        while True:
+            if rank == 0:
+                flag.fill_(1 if any(pr.poll() is None for pr in procs) else 0)
+            dist.broadcast(flag, 0)
+            if int(flag.item()) == 0:
+                break
+            t0 = time.perf_counter()
+            recs, counts = S.search(p, dq)        # incl. the D2H of the merged [64][10] records: an end-to-end batch
+            t_search += time.perf_counter() - t0
+            batches += 1
+            for i in range(NQ):                   # live parity, outside the timed part
+                live_bad += _unit_identity_violations(recs[i][:counts[i]])
+                live_hits += int(counts[i])
+        wall = time.perf_counter() - t_begin
+        stop.set()
+        th.join()
+        ops = sum(int(pr.communicate()[0].split()[0]) for pr in procs) if rank == 0 else 0
+        m.sync()                                   # quiesced: one more sweep and every shard equals its range of the store
+        dist.barrier()
+        recs, counts = S.search(p, dq)
+        mine = {"rank": rank, "attach_s": round(attach_s, 3), "syncs": len(syncs),
+                "sync_ms_median": round(float(np.median([x[0] for x in syncs])) * 1e3, 2) if syncs else None,
+                "rows_uploaded": int(sum(x[1] for x in syncs)), "skipped_busy": int(sum(x[2] for x in syncs)),
+                "live_hits_checked": live_hits, "live_violations": live_bad, "reissued_fp32": S.reissued}
+        allr = [None] * world
+        dist.all_gather_object(allr, mine)
+        if rank == 0:
+            ok = True
+            try:
+                for i in (0, 17, 63):              # merged cross-GPU answer == the CPU oracle over the whole store image
+                    ref, _ = support.oracle_search_image(img, q_host[i], K)
+                    assert counts[i] == len(ref)
+                    support.assert_topk_matches(recs[i][:counts[i]], ref)
+            except AssertionError as e:
+                ok = False
+                out["parity_error"] = str(e)[:200]
+            out.update({"parity_after_quiesce": ok, "parity_live": {"hits_checked": sum(r["live_hits_checked"] for r in allr),
+                                                                    "violations": sum(r["live_violations"] for r in allr)},
+                        "writer_processes": 4, "writer_ops_per_s": round(ops / SECONDS),
+                        "writer_mix": "80% set_embedding, 10% retrain_slot, 5% set/unset_label, 5% unset+set (reference API)",
+                        "sync_period_ms": PERIOD * 1e3, "batched_searches": batches,
+                        "ms_per_batch": round(t_search / max(batches, 1) * 1e3, 3),
+                        "queries_per_s": round(NQ * batches / max(t_search, 1e-9)),
+                        "queries_per_s_wall": round(NQ * batches / wall), "per_rank": allr})
+            return out
+        return None
+    finally:
+        if m is not None:
+            m.close()
+        dist.barrier()
+        if rank == 0 and os.path.exists(path):
+            os.unlink(path)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -515,6 +754,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs only)")
+    ap.add_argument("--skip-extra", action="store_true", help="omit the C4 anchor / C5 legs (profiling runs only)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -274,6 +274,17 @@ int spl_gpu_merge_topk_batch_device(spl_gpu_ctx *ctx, const spl_gpu_result *d_li
                                     uint32_t nlists, uint32_t nq, uint32_t list_stride, uint32_t order, uint32_t k,
                                     spl_gpu_result *d_out, uint32_t out_stride, uint32_t *d_out_counts, void *stream);
 
+/* The same merge over PACKED shard blocks, the form that needs one transfer (one all-gather, or one peer copy) per
+ * shard and batch instead of two: a shard's block is its [nq][list_stride] records followed by its [nq] counts,
+ * padded to a whole number of records -- SPL_GPU_PACKED_BLOCK_BYTES(nq, list_stride) bytes.  Point
+ * spl_gpu_search_device's d_out at the start of the block and its d_counts at SPL_GPU_PACKED_COUNTS_OFFSET bytes
+ * into it; d_packed = nlists such blocks back to back. */
+#define SPL_GPU_PACKED_COUNTS_OFFSET(nq, list_stride) ((size_t)(nq) * (list_stride) * 32u)
+#define SPL_GPU_PACKED_BLOCK_BYTES(nq, list_stride) (SPL_GPU_PACKED_COUNTS_OFFSET(nq, list_stride) + (((size_t)(nq) * 4u + 31u) & ~(size_t)31u))
+int spl_gpu_merge_topk_packed_device(spl_gpu_ctx *ctx, const void *d_packed, uint32_t nlists, uint32_t nq,
+                                     uint32_t list_stride, uint32_t order, uint32_t k, spl_gpu_result *d_out,
+                                     uint32_t out_stride, uint32_t *d_out_counts, void *stream);
+
 /* Allocation-free variant of the fused single-query scan.  (No counterpart in the reference; it
  * exists only because of how GPU memory is managed.)
  *

@@ -21,7 +21,7 @@ ABI_SYMBOLS = [
     "spl_gpu_last_error", "spl_gpu_sync", "spl_gpu_wait", "spl_gpu_dense_upload", "spl_gpu_dense_fill_synthetic",
     "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device", "spl_gpu_merge_topk_batch_device",
     "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
-    "spl_gpu_get_counters", "spl_gpu_find_key",
+    "spl_gpu_get_counters", "spl_gpu_find_key", "spl_gpu_merge_topk_packed_device",
 ]
 
 ORDER_COSINE, ORDER_L2 = 0, 1
@@ -114,6 +114,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_merge_topk_device.argtypes = [vp, vp, vp, u32, u32, u32, u32, vp, vp, vp]
     lib.spl_gpu_merge_topk_batch_device.restype = C.c_int
     lib.spl_gpu_merge_topk_batch_device.argtypes = [vp, vp, vp, u32, u32, u32, u32, u32, vp, u32, vp, vp]
+    lib.spl_gpu_merge_topk_packed_device.restype = C.c_int
+    lib.spl_gpu_merge_topk_packed_device.argtypes = [vp, vp, u32, u32, u32, u32, u32, vp, u32, vp, vp]
     lib.spl_gpu_scan_noalloc.restype = C.c_int
     lib.spl_gpu_scan_noalloc.argtypes = [vp, vp, vp, vp, u64, u64, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_slot_meta.restype = C.c_int
@@ -130,6 +132,16 @@ def load() -> C.CDLL:
     lib.spl_gpu_last_scan_ms.argtypes = [vp]
     _lib = lib
     return lib
+
+
+def packed_counts_offset(nq: int, stride: int) -> int:
+    """SPL_GPU_PACKED_COUNTS_OFFSET"""
+    return nq * stride * 32
+
+
+def packed_block_bytes(nq: int, stride: int) -> int:
+    """SPL_GPU_PACKED_BLOCK_BYTES: [nq][stride] records, then [nq] counts padded to a whole record"""
+    return packed_counts_offset(nq, stride) + ((nq * 4 + 31) & ~31)
 
 
 class SplinterGpuError(RuntimeError):
@@ -274,6 +286,11 @@ class Mirror:
         self._check(self._lib.spl_gpu_merge_topk_batch_device(self._h, C.c_void_p(d_lists), C.c_void_p(d_counts), nlists, nq,
                                                               stride, order, k, C.c_void_p(d_out), out_stride,
                                                               C.c_void_p(d_out_counts), C.c_void_p(stream)))
+
+    def merge_topk_packed_device(self, d_packed, nlists, nq, stride, order, k, d_out, out_stride, d_out_counts, stream=0):
+        self._check(self._lib.spl_gpu_merge_topk_packed_device(self._h, C.c_void_p(d_packed), nlists, nq, stride, order, k,
+                                                               C.c_void_p(d_out), out_stride, C.c_void_p(d_out_counts),
+                                                               C.c_void_p(stream)))
 
     def find_key(self, key: str):
         """slot index of `key` in the live store, or None"""

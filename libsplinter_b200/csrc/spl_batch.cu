@@ -42,6 +42,7 @@ constexpr int kStages = 4, kAcc = 2;
 constexpr int kThreadsGemm = 256;
 constexpr uint32_t kStageA = BM * BK * 2, kStageB = BN * BK * 2, kStageBytes = kStageA + kStageB;
 constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kExactBoundBlocks = 592;    // grid of exact_bound_kernel (4 per SM on a 148-SM part)
 constexpr uint32_t kMaxSampledTiles = 16384;  // pass-1 sample size cap (a power of two): 192 KB of sort space per query
 
 // ---- smem carve-up (dynamic, 1024-byte aligned for SWIZZLE_128B) ----
@@ -255,6 +256,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
         if (active) {
             const uint32_t t = threadIdx.x - 64;  // 0..63, four columns each
             const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+            // rows that score exactly (zero vector / no embedding) and have k' rows of their own kind before them can
+            // never be results: exact_bound_kernel found the row index of the k'-th of each kind
+            const uint32_t zero_bound = a.exact_bound[0], noemb_bound = a.exact_bound[1];
             uint32_t cs = 0, cph = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 const uint32_t row0 = (a.tile_first + j * a.tile_stride) * BN;
@@ -268,8 +272,12 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                         const bool pass = (f & need) && ((a.bloom[r] & a.mask) == a.mask) && r != a.exclude;
                         if (pass && (f & SPL_ROW_EMB)) {
                             const float n2 = a.norm2[r];
-                            if (a.order == SPL_ORDER_L2) { ca = -2.f; cb = n2; }
+                            if (n2 == 0.f && r > zero_bound && a.err2[r] == 0.f) {
+                                // a zero vector with k' zero vectors before it: same score, later index -- out
+                            } else if (a.order == SPL_ORDER_L2) { ca = -2.f; cb = n2; }
                             else { ca = n2 > 0.f ? -rsqrtf(n2) : 0.f; cb = 0.f; }
+                        } else if (pass && r > noemb_bound) {
+                            // likewise for rows without an embedding copy
                         } else if (pass) {
                             // no consistent embedding copy: scores like _search.c:388-391 (sim 0, dist FLT_MAX)
                             ca = 0.f; cb = a.order == SPL_ORDER_L2 ? 3.0e38f : 0.f;
@@ -344,7 +352,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                             } else if (t < INFINITY && t == thr) {
                                 // ties with the bound that the row index cut off: rows whose coefficient is 0 score exactly
                                 // (zero vector / no embedding), the others are ordinary rows that happen to tie in bf16
-                                out_tie |= pa[c0 + i] == 0.f ? 1u : 2u;
+                                // (coefficient 0: no embedding, or a zero vector in cosine order; L2 keeps -2 for every
+                                // embedded row, there a zero vector is the one whose norm term is 0)
+                                const bool exact_row = pa[c0 + i] == 0.f || (a.order == SPL_ORDER_L2 && pb[c0 + i] == 0.f);
+                                out_tie |= exact_row ? 1u : 2u;
                             } else {
                                 out_min = fminf(out_min, t);
                             }
@@ -378,6 +389,82 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
         tc_fence_after();
         if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
         else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// Rows whose score does not depend on the row's content -- a zero vector scores (0, |q|), a row without a consistent
+// embedding copy (0, FLT_MAX), _search.c:388-391 -- tie with every other row of their kind and are ordered by slot index
+// alone.  Only the first k' of each kind can ever be results, whatever the query.  The synthetic corpus of the benchmark
+// has 2 % never-embedded zero rows: without this cut every other 32-column chunk of the epilogue holds one, ties with the
+// bound and takes the slow per-element path.  bound[0] / bound[1] = row index of the k'-th zero / no-embedding row that
+// passes the candidate predicate (kIdxSentinel when there are fewer: keep them all).
+__device__ __forceinline__ uint32_t exact_kind(const BatchArgs &a, uint32_t r, uint32_t need) {   // 0 none, 1 zero, 2 no embedding
+    const uint32_t f = a.flags[r];
+    if (!(f & need) || (a.bloom[r] & a.mask) != a.mask || r == a.exclude) return 0;
+    if (!(f & SPL_ROW_EMB)) return 2;
+    return (a.norm2[r] == 0.f && a.err2[r] == 0.f) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256) exact_bound_kernel(const BatchArgs a, uint32_t kprime, uint32_t *__restrict__ counts,
+                                                          uint32_t *__restrict__ ticket, uint32_t *__restrict__ bound) {
+    __shared__ uint32_t s_cnt[2], s_last, s_blk[2], s_res[2], s_run, s_hit;
+    const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+    const uint32_t per = ((a.n + gridDim.x - 1) / gridDim.x + 255u) & ~255u;
+    const uint32_t lo = blockIdx.x * per, hi = min(a.n, lo + per);
+    if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t c1 = 0, c2 = 0;
+    for (uint32_t r = lo + threadIdx.x; r < hi; r += blockDim.x) {
+        const uint32_t kind = exact_kind(a, r, need);
+        c1 += kind == 1; c2 += kind == 2;
+    }
+    if (c1) atomicAdd(&s_cnt[0], c1);
+    if (c2) atomicAdd(&s_cnt[1], c2);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        counts[2 * blockIdx.x] = s_cnt[0]; counts[2 * blockIdx.x + 1] = s_cnt[1];
+        __threadfence();
+        s_last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < 2) {   // which block's range holds the k'-th row of this kind, and which one of its rows it is
+        uint32_t cum = 0, blk = kIdxSentinel, res = 0;
+        for (uint32_t b = 0; b < gridDim.x; b++) {
+            const uint32_t c = __ldcg(&counts[2 * b + threadIdx.x]);
+            if (cum + c >= kprime) { blk = b; res = kprime - cum; break; }
+            cum += c;
+        }
+        s_blk[threadIdx.x] = blk; s_res[threadIdx.x] = res;
+    }
+    if (threadIdx.x == 0) *ticket = 0;   // re-armed for the next batch
+    __syncthreads();
+    for (uint32_t kind = 1; kind <= 2; kind++) {
+        const uint32_t blk = s_blk[kind - 1], res = s_res[kind - 1];
+        if (blk == kIdxSentinel) { if (threadIdx.x == 0) bound[kind - 1] = kIdxSentinel; continue; }
+        if (threadIdx.x == 0) { s_run = 0; s_hit = kIdxSentinel; }
+        __syncthreads();
+        const uint32_t blo = blk * per, bhi = min(a.n, blo + per);
+        for (uint32_t base = blo; base < bhi && s_hit == kIdxSentinel; base += blockDim.x) {
+            const uint32_t r = base + threadIdx.x;
+            const bool is = r < bhi && exact_kind(a, r, need) == kind;
+            // rank of this row among the rows of its kind in [blo, ...): warp ballots + one shared running count
+            __shared__ uint32_t s_w[8];
+            const unsigned bal = __ballot_sync(0xffffffffu, is);
+            if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = __popc(bal);
+            __syncthreads();
+            uint32_t before = s_run;
+            for (uint32_t w = 0; w < (threadIdx.x >> 5); w++) before += s_w[w];
+            before += __popc(bal & ((1u << (threadIdx.x & 31)) - 1u));
+            if (is && before + 1 == res) s_hit = r;
+            __syncthreads();
+            if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < 8; w++) t += s_w[w]; s_run += t; }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) bound[kind - 1] = s_hit;
+        __syncthreads();
     }
 }
 
@@ -717,6 +804,12 @@ static cudaError_t launch_gemm(const CUtensorMap &mapQ, const CUtensorMap &mapE,
     return cudaLaunchKernelEx(&cfg, gemm_topk_kernel<true>, mapQ, mapE, a);
 }
 
+cudaError_t batch_scratch_init(BatchScratchLayout *L, unsigned char *scratch, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch + L->exact_off, 0, 16, s);
+    if (e == cudaSuccess) L->exact_armed = true;
+    return e;
+}
+
 bool batch_supported(uint32_t dim, uint32_t k) { return dim % BK == 0 && dim >= BK && k >= 1 && k <= 128; }
 
 size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, BatchScratchLayout *L) {
@@ -731,11 +824,13 @@ size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, Batch
     L->ovf_off = take((size_t)nq_pad * 4);
     L->out_min_off = take((size_t)nq_pad * 4);
     L->out_tie_off = take((size_t)nq_pad * 4);
+    L->exact_off = take((size_t)(4 + 2 * kExactBoundBlocks) * 4);   // bound[2], ticket, pad, counts[blocks][2]
     L->tile_min_off = take((size_t)tiles * nq_pad * 4);
     L->tile_min_row_off = take((size_t)tiles * nq_pad * 4);
     L->cand_t_off = take((size_t)nq_pad * kBatchCandCap * 4);
     L->cand_idx_off = take((size_t)nq_pad * kBatchCandCap * 4);
     L->nq_pad = nq_pad;
+    L->exact_armed = false;
     return off;
 }
 
@@ -775,6 +870,13 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     if ((e = cudaMemsetAsync(a.out_min, 0xFF, (size_t)a.nq_pad * 4, s))) return e;
     if ((e = cudaMemsetAsync(a.out_tie, 0, (size_t)a.nq_pad * 4, s))) return e;
 
+    {   // per-kind bounds for the rows that score exactly (see exact_bound_kernel); the ticket re-arms itself
+        uint32_t *ex = reinterpret_cast<uint32_t *>(scratch + L.exact_off);
+        a.exact_bound = ex;
+        if (!L.exact_armed) return cudaErrorInvalidValue;   // the ticket word must have been zeroed once (batch_scratch_init)
+        exact_bound_kernel<<<kExactBoundBlocks, 256, 0, s>>>(a, kprime, ex + 4, ex + 2, ex);
+        if ((e = cudaGetLastError())) return e;
+    }
     const uint32_t tiles = (a.n + BN - 1) / BN;
     int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;
     if (grid < (int)a.n_qtiles) grid = (int)a.n_qtiles;
@@ -791,7 +893,15 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     a.pass = 1; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = sampled;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
-    threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, kprime, a.thr,
+    // Which order statistic of the sampled tile minima becomes the bound: the list should hold about 16 k' entries, so
+    // that a crowd of near-ties around the k-th score is IN the list (the selection proof can then re-score it) and
+    // the rows left out are far enough from the k-th for the proof's bound to clear them.  With a 1/f sample the
+    // k'-th smallest minimum already sits near rank f k' of the shard; a small shard that is sampled whole needs a
+    // later one (but no later than half of its tiles: one candidate per tile is all the minima can vouch for).
+    uint32_t thr_rank = (uint32_t)(((uint64_t)16 * kprime * sampled + tiles - 1) / tiles);
+    if (thr_rank > sampled / 2) thr_rank = sampled / 2;
+    if (thr_rank < kprime) thr_rank = kprime;
+    threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, thr_rank, a.thr,
                                                        a.thr_row);
     if ((e = cudaGetLastError())) return e;
     // pass 2: every tile, append what beats the threshold
@@ -800,7 +910,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     const size_t sel_smem = (size_t)kBatchCandCap * 12;   // opted in by batch_prepare()
     select_rerank_kernel<<<a.nq, 256, sel_smem, s>>>(a, d_q32, k, kprime, d_out, out_stride, d_counts, overflow);
     if ((e = cudaGetLastError())) return e;
-    *launches = 5;
+    *launches = 6;
     return cudaSuccess;
 }
 

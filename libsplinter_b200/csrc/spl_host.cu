@@ -1014,6 +1014,8 @@ static int ensure_batch_scratch(spl_gpu_ctx *c, uint32_t k) {
         const size_t bytes = batch_scratch_bytes((uint32_t)c->n, kBatchMaxQ, c->dim, &c->batch_layout);
         if ((rc = dev_alloc(c, &c->d_batch, bytes, false))) return rc;
         if ((rc = dev_alloc(c, &c->d_qbatch, (size_t)kBatchMaxQ * c->dim, false))) return rc;
+        CUDA_TRY(batch_scratch_init(&c->batch_layout, c->d_batch, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));   // the first batch may run on a caller's stream
     }
     const uint32_t need = kBatchMaxQ * k;
     if (c->bout_cap < need) {
@@ -1349,6 +1351,25 @@ extern "C" int spl_gpu_merge_topk_batch_device(spl_gpu_ctx *c, const spl_gpu_res
     cudaSetDevice(c->device);
     CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, nq, list_stride, order, k, d_out, out_stride, d_out_counts,
                                   stream ? (cudaStream_t)stream : c->stream));
+    c->launches++;
+    return 0;
+}
+
+extern "C" int spl_gpu_merge_topk_packed_device(spl_gpu_ctx *c, const void *d_packed, uint32_t nlists, uint32_t nq,
+                                                uint32_t list_stride, uint32_t order, uint32_t k, spl_gpu_result *d_out,
+                                                uint32_t out_stride, uint32_t *d_out_counts, void *stream) {
+    if (!c || !d_packed || !d_out || !d_out_counts) return fail(-2, EINVAL, "null argument");
+    if (k == 0 || k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "merge needs k in 1..%u", SPL_GPU_KMAX_FUSED);
+    if (order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order");
+    if (nq == 0 || out_stride < k || list_stride == 0) return fail(-2, EINVAL, "merge needs nq >= 1, list_stride >= 1 and out_stride >= k");
+    const size_t block = SPL_GPU_PACKED_BLOCK_BYTES(nq, list_stride);
+    const unsigned char *base = static_cast<const unsigned char *>(d_packed);
+    cudaSetDevice(c->device);
+    CUDA_TRY(launch_merge_results(reinterpret_cast<const spl_gpu_result *>(base),
+                                  reinterpret_cast<const uint32_t *>(base + SPL_GPU_PACKED_COUNTS_OFFSET(nq, list_stride)), nlists, nq,
+                                  list_stride, order, k, d_out, out_stride, d_out_counts,
+                                  stream ? (cudaStream_t)stream : c->stream, (uint32_t)(block / sizeof(spl_gpu_result)),
+                                  (uint32_t)(block / sizeof(uint32_t))));
     c->launches++;
     return 0;
 }

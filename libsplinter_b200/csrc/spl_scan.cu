@@ -277,12 +277,14 @@ cudaError_t launch_scan_fast(const ScanArgs &a, int grid, cudaStream_t stream) {
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t kMergeMaxEntries = 8192;  // nlists * stride candidates per call (96 KB of smem)
 
-// One CTA per query.  Gathered layout: lists[shard][query][stride] records, counts[shard][query]; with nq = 1 that is
-// simply nlists consecutive lists.  Output: out[query][out_stride], out_count[query].
+// One CTA per query.  Gathered layout: shard s holds its [query][stride] records at lists + s * shard_pitch (records) and
+// its [query] counts at counts + s * count_pitch (uint32s): shard_pitch = nq * stride, count_pitch = nq for two separate
+// contiguous arrays; the packed form (records then counts in ONE block per shard, so one transfer per shard suffices)
+// uses the block size for both.  Output: out[query][out_stride], out_count[query].
 __global__ void __launch_bounds__(1024, 1)
 merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t nq, uint32_t stride,
-                     uint32_t order, uint32_t k, uint32_t entries, spl_gpu_result *out, uint32_t out_stride,
-                     uint32_t *out_count) {
+                     uint32_t shard_pitch, uint32_t count_pitch, uint32_t order, uint32_t k, uint32_t entries,
+                     spl_gpu_result *out, uint32_t out_stride, uint32_t *out_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
     uint32_t *slot = reinterpret_cast<uint32_t *>(keys + entries);
@@ -296,7 +298,7 @@ merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32
     if (threadIdx.x == 0) s_unanswered = 0;
     __syncthreads();
     for (uint32_t l = threadIdx.x; l < nlists; l += blockDim.x)
-        if (counts[(size_t)l * nq + q] == SPL_GPU_COUNT_UNANSWERED) s_unanswered = 1;
+        if (counts[(size_t)l * count_pitch + q] == SPL_GPU_COUNT_UNANSWERED) s_unanswered = 1;
     __syncthreads();
     if (s_unanswered) {
         if (threadIdx.x == 0) *out_count = SPL_GPU_COUNT_UNANSWERED;
@@ -306,8 +308,8 @@ merge_results_kernel(const spl_gpu_result *lists, const uint32_t *counts, uint32
         const uint32_t l = p / stride, i = p - l * stride;
         uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
         uint32_t src = 0;
-        if (l < nlists && i < min(counts[(size_t)l * nq + q], stride)) {
-            src = (uint32_t)(((size_t)l * nq + q) * stride + i);
+        if (l < nlists && i < min(counts[(size_t)l * count_pitch + q], stride)) {
+            src = (uint32_t)((size_t)l * shard_pitch + (size_t)q * stride + i);
             const spl_gpu_result r = lists[src];
             key = make_key(order, r.similarity, r.distance);
             id = r.slot_idx;  // ties between shards break on the GLOBAL slot index
@@ -333,13 +335,14 @@ cudaError_t merge_prepare() {
 
 cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t nq,
                                  uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out, uint32_t out_stride,
-                                 uint32_t *out_count, cudaStream_t stream) {
+                                 uint32_t *out_count, cudaStream_t stream, uint32_t shard_pitch, uint32_t count_pitch) {
     const uint32_t entries = topk_pow2(nlists * stride > k ? nlists * stride : k + 1);
     if (entries > kMergeMaxEntries || nq == 0) return cudaErrorInvalidValue;
+    if (shard_pitch == 0) { shard_pitch = nq * stride; count_pitch = nq; }
     const size_t smem = (size_t)entries * 16;
     const int threads = entries >= 2048 ? 1024 : (entries >= 512 ? 256 : 128);
-    merge_results_kernel<<<nq, threads, smem, stream>>>(lists, counts, nlists, nq, stride, order, k, entries, out, out_stride,
-                                                       out_count);
+    merge_results_kernel<<<nq, threads, smem, stream>>>(lists, counts, nlists, nq, stride, shard_pitch, count_pitch, order, k,
+                                                       entries, out, out_stride, out_count);
     return cudaGetLastError();
 }
 

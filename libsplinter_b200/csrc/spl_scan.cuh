@@ -66,10 +66,11 @@ cudaError_t scan_tma_prepare();
 cudaError_t launch_scan_tma(const ScanArgs &a, int grid, cudaStream_t stream);
 
 cudaError_t merge_prepare();
-// merge nlists lists of Cand-like results (spl_gpu_result records) into the top-k
+// merge nlists lists of Cand-like results (spl_gpu_result records) into the top-k; shard_pitch (records) / count_pitch
+// (uint32s) = distance between consecutive shards' blocks, 0 = two separate contiguous arrays
 cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *counts, uint32_t nlists, uint32_t nq,
                                  uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out, uint32_t out_stride,
-                                 uint32_t *out_count, cudaStream_t stream);
+                                 uint32_t *out_count, cudaStream_t stream, uint32_t shard_pitch = 0, uint32_t count_pitch = 0);
 
 // unlimited / k > SPL_GPU_KMAX_FUSED: sort (key, row) pairs of a whole shard and emit records.
 // keys[n] holds the scan's output; tmp buffers are caller-allocated (see sortall_tmp_bytes).

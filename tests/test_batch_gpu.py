@@ -61,15 +61,15 @@ def test_batched_small_shapes_and_auto_mode():
         ref, rc = support.oracle_search_dense(q16, E, bloom, flags, k=10)
         for i in range(20):
             support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
-        # which path AUTO takes, seen through the launch counter (batched = 5 launches per call, scan = one per
+        # which path AUTO takes, seen through the launch counter (batched = 6 launches per call, scan = one per
         # group of up to 4 queries): unfiltered batches go to the tensor cores from 4 queries, masked ones from 16
         def launches(nq, **kw):
             before = m.launch_count()
             m.search(q16[:nq], 10, **kw)
             return m.launch_count() - before
-        assert launches(4) == 5 and launches(3) == 2                     # 3 queries: a 2-query and a 1-query scan
+        assert launches(4) == 6 and launches(3) == 2                     # 3 queries: a 2-query and a 1-query scan
         assert launches(4, bloom_mask=0x1) == 1 and launches(15, bloom_mask=0x1) == 5   # 4+4+4+2+1
-        assert launches(16, bloom_mask=0x1) == 5
+        assert launches(16, bloom_mask=0x1) == 6
         assert launches(20, max_distance=1.0) == 5                       # cosine order + distance threshold: 5 scans of 4
     finally:
         m.close()
@@ -174,11 +174,11 @@ def _near_duplicate_corpus(n, dim, ndup, noise, seed):
 
 
 @pytest.mark.parametrize("dim", [768, 1024])
-@pytest.mark.parametrize("ndup,noise", [(3000, 1e-2), (10_000, 1e-3), (3000, 1e-4), (200, 1e-2)])
+@pytest.mark.parametrize("ndup,noise", [(3000, 1e-2), (10_000, 1e-3), (3000, 1e-4), (100, 1e-2)])
 def test_near_duplicates_do_not_fool_the_bf16_selection(dim, ndup, noise):
     """The bf16 pass only PROPOSES rows; the selection proof in select_rerank_kernel decides whether the proposal can
     be trusted.  With thousands of rows packed inside one bf16 error bound of the k-th score it cannot, and the query
-    goes to the fp32 scan; with a couple of hundred the kernel re-scores them all itself.  Either way the answer is
+    goes to the fp32 scan; with a hundred the kernel re-scores them all itself.  Either way the answer is
     the reference's: same indices (where fp32 itself separates the rows), both orders, with and without a mask."""
     n, k = 60_000, 32
     E, bloom, q = _near_duplicate_corpus(n, dim, ndup, noise, seed=ndup + dim)
@@ -204,7 +204,8 @@ def test_near_duplicates_do_not_fool_the_bf16_selection(dim, ndup, noise):
                     assert c1.batch_unproven > c0.batch_unproven
                 else:               # a small crowd is re-scored inside the kernel, nothing falls back
                     assert c1.batch_unproven == c0.batch_unproven
-                    assert c1.batch_rescored_extra > c0.batch_rescored_extra
+                    if mask == 0:   # (with the mask only half of the crowd are candidates: they fit into the fixed 2k)
+                        assert c1.batch_rescored_extra > c0.batch_rescored_extra
 
 
 def test_random_corpus_needs_no_fallback():

@@ -78,6 +78,58 @@ WORKER = textwrap.dedent("""
         m = support.oracle().splo_merge_topk(support._p(flat), support._p(gc[:, qi].astype(np.uint32).copy()), world, K, 0, K,
                                              support._p(out))
         ok &= (m == fc[qi]) and np.array_equal(out[:m]["idx"], full[qi][:m]["idx"])
+    # ---- ShardedSearcher: packed blocks, ONE gather per batch, and the re-issue of a query a shard could not answer ----
+    import ctypes as C
+    from libsplinter_b200.sharding import ShardedSearcher
+    from libsplinter_b200.binding import (COUNT_UNANSWERED, MODE_BATCH_BF16, MODE_FAST, SearchParams, packed_block_bytes,
+                                          packed_counts_offset)
+    calls = dict(search=0, gathers=0)
+    real_gather = dist.all_gather_into_tensor
+    def counting_gather(*a, **kw):
+        calls["gathers"] += 1
+        return real_gather(*a, **kw)
+    dist.all_gather_into_tensor = counting_gather
+    def search_fn(params, qt, block):
+        nq = int(params.nq)
+        calls["search"] += 1
+        loc, lc = support.oracle_search_dense(qt.numpy(), E, bloom, flags, k=K, bloom_mask=int(params.bloom_mask))
+        raw = block.numpy()
+        raw[:] = 0
+        recs = raw[:nq * K * 32].view(RESULT_DTYPE).reshape(nq, K)
+        for i in range(nq):
+            n = int(lc[i])
+            recs[i]["slot_idx"][:n] = loc[i]["idx"][:n] + lo
+            recs[i]["similarity"][:n] = loc[i]["similarity"][:n]
+            recs[i]["distance"][:n] = loc[i]["distance"][:n]
+        cnts = raw[packed_counts_offset(nq, K):packed_counts_offset(nq, K) + 4 * nq].view(np.uint32)
+        cnts[:] = lc
+        if int(params.mode) != MODE_FAST and rank == world - 1:
+            cnts[1] = COUNT_UNANSWERED          # pretend this shard's bf16 pass could not prove query 1
+    def merge_fn(gathered, nq, fin, fcnt):
+        blk_bytes = packed_block_bytes(nq, K)
+        g = gathered.numpy().reshape(world, blk_bytes)
+        outr = fin.numpy().reshape(nq, K * 32).view(RESULT_DTYPE).reshape(nq, K)
+        for i in range(nq):
+            cs = np.array([g[w][packed_counts_offset(nq, K):].view(np.uint32)[i] for w in range(world)], np.uint32)
+            if (cs == COUNT_UNANSWERED).any():
+                fcnt[i] = -1                    # the marker, as the int32 the tensor holds
+                continue
+            flat = np.zeros((world, K), support.SPLO_RESULT)
+            for w in range(world):
+                r = g[w][:nq * K * 32].view(RESULT_DTYPE).reshape(nq, K)[i]
+                flat[w]["idx"] = r["slot_idx"]; flat[w]["similarity"] = r["similarity"]; flat[w]["distance"] = r["distance"]
+            mo = np.zeros(K, support.SPLO_RESULT)
+            mm = support.oracle().splo_merge_topk(support._p(flat), support._p(cs), world, K, 0, K, support._p(mo))
+            outr[i]["slot_idx"][:mm] = mo["idx"][:mm]; outr[i]["similarity"][:mm] = mo["similarity"][:mm]
+            outr[i]["distance"][:mm] = mo["distance"][:mm]
+            fcnt[i] = int(mm)
+    S = ShardedSearcher(None, world, 3, K, 0, "cpu", search_fn=search_fn, merge_fn=merge_fn)
+    prm = SearchParams(C.sizeof(SearchParams), 3, DIM, K, 0, MODE_BATCH_BF16, 1, 0.0, 0.0, 0xFFFFFFFF, 0)
+    recs, cnts = S.search(prm, torch.from_numpy(q))
+    for qi in range(3):
+        ok &= int(cnts[qi]) == int(fc[qi]) and np.array_equal(recs[qi][:cnts[qi]]["slot_idx"], full[qi][:fc[qi]]["idx"])
+    ok &= S.reissued == 1 and calls["search"] == 2        # one batched pass + one fp32 re-issue of query 1, on every rank
+    ok &= calls["gathers"] == (2 if world > 1 else 0)     # ONE collective per pass
     flag = torch.tensor([1 if ok else 0])
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

@@ -53,28 +53,37 @@ def one_shot(binary, name, qfile, flags, reps):
 
 
 def repl_session(binary, name, qfile, flags, nqueries):
+    """Type nqueries searches into ONE REPL process and time each from the keystroke to the closing brace of its JSON.
+    The child's stdout is a pty so that its libc flushes line by line (into a pipe it would hold everything back
+    until exit)."""
+    import pty
+    import select
     stub = subprocess.Popen([str(REF / "ref_embed_stub"), name, qfile, "120000", str(nqueries)])
-    p = subprocess.Popen([str(binary), "--use", name], stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
-                         text=True, bufsize=1)
+    master, slave = pty.openpty()
+    p = subprocess.Popen([str(binary), "--use", name], stdin=subprocess.PIPE, stdout=slave, stderr=subprocess.DEVNULL)
+    os.close(slave)
     times, outs = [], []
-    line = 'search "what is splinter?" ' + " ".join(flags) + " --json\n"
-    for _ in range(nqueries):
-        t0 = time.perf_counter()
-        p.stdin.write(line)
-        p.stdin.flush()
-        buf = []
-        while True:
-            ln = p.stdout.readline()
-            if not ln:
-                raise RuntimeError("REPL closed its output")
-            buf.append(ln)
-            if ln == "}\n":
-                break
-        times.append((time.perf_counter() - t0) * 1e3)
-        outs.append("".join(buf))
-    p.stdin.close()
-    p.wait(timeout=60)
-    stub.wait(timeout=60)
+    line = ('search "what is splinter?" ' + " ".join(flags) + " --json\n").encode()
+    try:
+        for _ in range(nqueries):
+            t0 = time.perf_counter()
+            p.stdin.write(line)
+            p.stdin.flush()
+            buf = b""
+            while not buf.replace(b"\r\n", b"\n").endswith(b"\n}\n"):
+                r, _, _ = select.select([master], [], [], 120)
+                if not r:
+                    raise RuntimeError("REPL did not answer within 120 s: " + buf[-200:].decode(errors="replace"))
+                buf += os.read(master, 65536)
+            times.append((time.perf_counter() - t0) * 1e3)
+            outs.append(buf.replace(b"\r\n", b"\n").decode())
+        p.stdin.close()
+        p.wait(timeout=60)
+    finally:
+        if p.poll() is None:
+            p.kill()
+        os.close(master)
+        stub.wait(timeout=130)
     return times, outs
 
 
