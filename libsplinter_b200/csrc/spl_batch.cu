@@ -42,7 +42,6 @@ constexpr int kStages = 4, kAcc = 2;
 constexpr int kThreadsGemm = 256;
 constexpr uint32_t kStageA = BM * BK * 2, kStageB = BN * BK * 2, kStageBytes = kStageA + kStageB;
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kExactBoundBlocks = 592;    // grid of exact_bound_kernel (4 per SM on a 148-SM part)
 constexpr uint32_t kMaxSampledTiles = 16384;  // pass-1 sample size cap (a power of two): 192 KB of sort space per query
 
 // ---- smem carve-up (dynamic, 1024-byte aligned for SWIZZLE_128B) ----
@@ -258,11 +257,13 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
             const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
             // rows that score exactly (zero vector / no embedding) and have k' rows of their own kind before them can
             // never be results: exact_bound_kernel found the row index of the k'-th of each kind
-            const uint32_t zero_bound = a.exact_bound[0], noemb_bound = a.exact_bound[1];
+            const uint32_t zero_bound = a.pass == 2 ? a.exact_bound[0] : kIdxSentinel;
+            const uint32_t noemb_bound = a.pass == 2 ? a.exact_bound[1] : kIdxSentinel;
             uint32_t cs = 0, cph = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 const uint32_t row0 = (a.tile_first + j * a.tile_stride) * BN;
                 float va[4], vb[4];
+                uint32_t nzero = 0, nnoemb = 0;   // pass 1: candidates of either exactly-scoring kind in this tile
 #pragma unroll
                 for (int i = 0; i < 4; i++) {
                     const uint32_t r = row0 + t + 64 * i;
@@ -272,18 +273,29 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                         const bool pass = (f & need) && ((a.bloom[r] & a.mask) == a.mask) && r != a.exclude;
                         if (pass && (f & SPL_ROW_EMB)) {
                             const float n2 = a.norm2[r];
-                            if (n2 == 0.f && r > zero_bound && a.err2[r] == 0.f) {
+                            const bool zero_row = n2 == 0.f && a.err2[r] == 0.f;
+                            nzero += zero_row;
+                            if (zero_row && r > zero_bound) {
                                 // a zero vector with k' zero vectors before it: same score, later index -- out
                             } else if (a.order == SPL_ORDER_L2) { ca = -2.f; cb = n2; }
                             else { ca = n2 > 0.f ? -rsqrtf(n2) : 0.f; cb = 0.f; }
                         } else if (pass && r > noemb_bound) {
-                            // likewise for rows without an embedding copy
+                            nnoemb++;   // likewise for rows without an embedding copy
                         } else if (pass) {
+                            nnoemb++;
                             // no consistent embedding copy: scores like _search.c:388-391 (sim 0, dist FLT_MAX)
                             ca = 0.f; cb = a.order == SPL_ORDER_L2 ? 3.0e38f : 0.f;
                         }
                     }
                     va[i] = ca; vb[i] = cb;
+                }
+                if (a.pass == 1 && qtile == 0) {   // every query tile sees the same rows: one of them counts
+                    nzero = __reduce_add_sync(0xffffffffu, nzero);
+                    nnoemb = __reduce_add_sync(0xffffffffu, nnoemb);
+                    if (lane == 0 && (nzero | nnoemb)) {
+                        if (nzero) atomicAdd(&a.tile_kinds[2 * j], nzero);
+                        if (nnoemb) atomicAdd(&a.tile_kinds[2 * j + 1], nnoemb);
+                    }
                 }
                 bar_wait(CEMPTY(cs), cph ^ 1u);
 #pragma unroll
@@ -321,7 +333,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                     tc_ld32(tmem_base + ((quad * 32u) << 16) + acc * BN + c0, v);
                     const float4 *pa4 = reinterpret_cast<const float4 *>(pa + c0), *pb4 = reinterpret_cast<const float4 *>(pb + c0);
                     // branch-free common path: ordering values + their minimum over the 32 columns
-                    float cmin = INFINITY;
+                    float gmin[8];   // minimum of each group of four columns: the slow path below looks only into groups that hit
 #pragma unroll
                     for (int i4 = 0; i4 < 8; i4++) {
                         const float4 ca = pa4[i4], cb = pb4[i4];
@@ -329,8 +341,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                         float t2 = fmaf(__uint_as_float(v[4 * i4 + 2]), ca.z, cb.z), t3 = fmaf(__uint_as_float(v[4 * i4 + 3]), ca.w, cb.w);
                         v[4 * i4 + 0] = __float_as_uint(t0); v[4 * i4 + 1] = __float_as_uint(t1);
                         v[4 * i4 + 2] = __float_as_uint(t2); v[4 * i4 + 3] = __float_as_uint(t3);
-                        cmin = fminf(cmin, fminf(fminf(t0, t1), fminf(t2, t3)));
+                        gmin[i4] = fminf(fminf(t0, t1), fminf(t2, t3));
                     }
+                    const float cmin = fminf(fminf(fminf(gmin[0], gmin[1]), fminf(gmin[2], gmin[3])),
+                                             fminf(fminf(gmin[4], gmin[5]), fminf(gmin[6], gmin[7])));
                     if (a.pass == 1) {
                         if (cmin < tmin) {   // rare after the first few tiles: find the first column holding the new minimum
                             tmin = cmin;
@@ -338,8 +352,14 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                             for (int i = 31; i >= 0; i--) if (__uint_as_float(v[i]) == cmin) imin = row0 + c0 + i;
                         }
                     } else if (cmin <= thr) {  // some column of this chunk may beat the bound (static register indexing)
+                        // A thread takes this path for a few percent of its chunks, but a WARP (32 queries) for most of them:
+                        // what the whole warp pays must stay small, so only the groups of four that hit are opened.
 #pragma unroll
-                        for (int i = 0; i < 32; i++) {
+                        for (int j = 0; j < 8; j++) {
+                          if (gmin[j] > thr) { out_min = fminf(out_min, gmin[j]); continue; }
+#pragma unroll
+                          for (int e4 = 0; e4 < 4; e4++) {
+                            const int i = 4 * j + e4;
                             const float t = __uint_as_float(v[i]);
                             // t = +inf marks a row that is not a candidate (or lies past the shard's end); it must stay out
                             // even when the bound itself is +inf (fewer sampled tiles than k')
@@ -359,6 +379,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                             } else {
                                 out_min = fminf(out_min, t);
                             }
+                          }
                         }
                     } else {
                         out_min = fminf(out_min, cmin);   // the whole chunk stays out: remember the best value left out
@@ -397,75 +418,15 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
 // embedding copy (0, FLT_MAX), _search.c:388-391 -- tie with every other row of their kind and are ordered by slot index
 // alone.  Only the first k' of each kind can ever be results, whatever the query.  The synthetic corpus of the benchmark
 // has 2 % never-embedded zero rows: without this cut every other 32-column chunk of the epilogue holds one, ties with the
-// bound and takes the slow per-element path.  bound[0] / bound[1] = row index of the k'-th zero / no-embedding row that
-// passes the candidate predicate (kIdxSentinel when there are fewer: keep them all).
+// bound and takes the slow per-element path.  Pass 1 (the sampled PREFIX of tiles) counts, per tile, the rows of either
+// kind that pass the candidate predicate; exact_bound_block (an extra block of threshold_kernel) turns the counts into
+// bound[0] / bound[1] = row index of the k'-th zero / no-embedding candidate, or kIdxSentinel when the prefix holds fewer
+// than k' of them (then all are kept: correct, merely not pruned).  Pass 2 drops rows of a kind beyond its bound.
 __device__ __forceinline__ uint32_t exact_kind(const BatchArgs &a, uint32_t r, uint32_t need) {   // 0 none, 1 zero, 2 no embedding
     const uint32_t f = a.flags[r];
     if (!(f & need) || (a.bloom[r] & a.mask) != a.mask || r == a.exclude) return 0;
     if (!(f & SPL_ROW_EMB)) return 2;
     return (a.norm2[r] == 0.f && a.err2[r] == 0.f) ? 1u : 0u;
-}
-
-__global__ void __launch_bounds__(256) exact_bound_kernel(const BatchArgs a, uint32_t kprime, uint32_t *__restrict__ counts,
-                                                          uint32_t *__restrict__ ticket, uint32_t *__restrict__ bound) {
-    __shared__ uint32_t s_cnt[2], s_last, s_blk[2], s_res[2], s_run, s_hit;
-    const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
-    const uint32_t per = ((a.n + gridDim.x - 1) / gridDim.x + 255u) & ~255u;
-    const uint32_t lo = blockIdx.x * per, hi = min(a.n, lo + per);
-    if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
-    __syncthreads();
-    uint32_t c1 = 0, c2 = 0;
-    for (uint32_t r = lo + threadIdx.x; r < hi; r += blockDim.x) {
-        const uint32_t kind = exact_kind(a, r, need);
-        c1 += kind == 1; c2 += kind == 2;
-    }
-    if (c1) atomicAdd(&s_cnt[0], c1);
-    if (c2) atomicAdd(&s_cnt[1], c2);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        counts[2 * blockIdx.x] = s_cnt[0]; counts[2 * blockIdx.x + 1] = s_cnt[1];
-        __threadfence();
-        s_last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    if (threadIdx.x < 2) {   // which block's range holds the k'-th row of this kind, and which one of its rows it is
-        uint32_t cum = 0, blk = kIdxSentinel, res = 0;
-        for (uint32_t b = 0; b < gridDim.x; b++) {
-            const uint32_t c = __ldcg(&counts[2 * b + threadIdx.x]);
-            if (cum + c >= kprime) { blk = b; res = kprime - cum; break; }
-            cum += c;
-        }
-        s_blk[threadIdx.x] = blk; s_res[threadIdx.x] = res;
-    }
-    if (threadIdx.x == 0) *ticket = 0;   // re-armed for the next batch
-    __syncthreads();
-    for (uint32_t kind = 1; kind <= 2; kind++) {
-        const uint32_t blk = s_blk[kind - 1], res = s_res[kind - 1];
-        if (blk == kIdxSentinel) { if (threadIdx.x == 0) bound[kind - 1] = kIdxSentinel; continue; }
-        if (threadIdx.x == 0) { s_run = 0; s_hit = kIdxSentinel; }
-        __syncthreads();
-        const uint32_t blo = blk * per, bhi = min(a.n, blo + per);
-        for (uint32_t base = blo; base < bhi && s_hit == kIdxSentinel; base += blockDim.x) {
-            const uint32_t r = base + threadIdx.x;
-            const bool is = r < bhi && exact_kind(a, r, need) == kind;
-            // rank of this row among the rows of its kind in [blo, ...): warp ballots + one shared running count
-            __shared__ uint32_t s_w[8];
-            const unsigned bal = __ballot_sync(0xffffffffu, is);
-            if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = __popc(bal);
-            __syncthreads();
-            uint32_t before = s_run;
-            for (uint32_t w = 0; w < (threadIdx.x >> 5); w++) before += s_w[w];
-            before += __popc(bal & ((1u << (threadIdx.x & 31)) - 1u));
-            if (is && before + 1 == res) s_hit = r;
-            __syncthreads();
-            if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < 8; w++) t += s_w[w]; s_run += t; }
-            __syncthreads();
-        }
-        if (threadIdx.x == 0) bound[kind - 1] = s_hit;
-        __syncthreads();
-    }
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -481,12 +442,46 @@ __global__ void __launch_bounds__(256) qprep_kernel(const float *__restrict__ q,
 }
 
 // thr[q] = k'-th smallest tile minimum over the sampled tiles (+inf if fewer than k' finite ones)
+// One block: from the per-tile counts pass 1 left in tile_kinds, the row index of the k'-th candidate of either
+// exactly-scoring kind (tiles of the prefix are consecutive: tile j = rows [256 j, 256 j + 256)).
+__device__ void exact_bound_block(const BatchArgs &a, uint32_t n_tiles, uint32_t kprime) {
+    __shared__ uint32_t s_tile[2], s_res[2], s_w[8], s_run;
+    const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
+    if (threadIdx.x < 2) {
+        uint32_t cum = 0, tile = kIdxSentinel, res = 0;
+        for (uint32_t j = 0; j < n_tiles; j++) {    // (a few thousand L2 hits at worst; the k'-th is usually in the first tiles)
+            const uint32_t c = a.tile_kinds[2 * j + threadIdx.x];
+            if (cum + c >= kprime) { tile = j; res = kprime - cum; break; }
+            cum += c;
+        }
+        s_tile[threadIdx.x] = tile; s_res[threadIdx.x] = res;
+    }
+    __syncthreads();
+    for (uint32_t kind = 1; kind <= 2; kind++) {
+        const uint32_t tile = s_tile[kind - 1], res = s_res[kind - 1];
+        if (tile == kIdxSentinel) { if (threadIdx.x == 0) a.exact_bound_out[kind - 1] = kIdxSentinel; continue; }
+        const uint32_t r = tile * BN + threadIdx.x;           // blockDim.x == BN == 256: one row per thread
+        const bool is = r < a.n && exact_kind(a, r, need) == kind;
+        const unsigned bal = __ballot_sync(0xffffffffu, is);
+        if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = __popc(bal);
+        __syncthreads();
+        uint32_t before = 0;
+        for (uint32_t w = 0; w < (threadIdx.x >> 5); w++) before += s_w[w];
+        before += __popc(bal & ((1u << (threadIdx.x & 31)) - 1u));
+        if (is && before + 1 == res) a.exact_bound_out[kind - 1] = r;
+        __syncthreads();
+    }
+    (void)s_run;
+}
+
 __global__ void __launch_bounds__(256) threshold_kernel(const float *__restrict__ tile_min, const uint32_t *__restrict__ tile_min_row,
                                                         uint32_t n_tiles, uint32_t nq, uint32_t nq_pad, uint32_t kprime,
-                                                        float *__restrict__ thr, uint32_t *__restrict__ thr_row) {
+                                                        float *__restrict__ thr, uint32_t *__restrict__ thr_row,
+                                                        const BatchArgs ba, uint32_t kprime_exact) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
     const uint32_t q = blockIdx.x;
+    if (q == nq) { exact_bound_block(ba, n_tiles, kprime_exact); return; }
     const uint32_t P = next_pow2(n_tiles < 2 ? 2 : n_tiles);
     uint32_t *idx = reinterpret_cast<uint32_t *>(keys + P);
     for (uint32_t i = threadIdx.x; i < P; i += blockDim.x) {
@@ -535,23 +530,58 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
         if (threadIdx.x == 0) { overflow[q] = 1; out_count[q] = SPL_GPU_COUNT_UNANSWERED; }
         return;
     }
-    const uint32_t P = next_pow2(total < 2 ? 2 : total);
-    uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *idx = reinterpret_cast<uint32_t *>(keys + P);
-    for (uint32_t i = threadIdx.x; i < P; i += blockDim.x) {
-        uint64_t key = kKeySentinel; uint32_t id = kIdxSentinel;
-        if (i < total) { key = f2ord(a.cand_t[(size_t)q * a.cand_cap + i]); id = a.cand_idx[(size_t)q * a.cand_cap + i]; }
-        keys[i] = key; idx[i] = id;
-    }
-    __syncthreads();
-    bitonic_sort_cta(keys, idx, P);
+    // The list is NOT sorted as a whole (a bitonic sort of ~1000 entries per query was the bulk of this kernel): only
+    // its m best entries by (t, row) are needed in order, the rest are merely visited by the proof below.  A radix
+    // select (8 passes of 8 bits over the 64-bit composite f2ord(t) << 32 | row, which is unique per row) finds the
+    // m-th smallest composite; the entries up to it are compacted into the re-score area.
+    uint64_t *ckey = reinterpret_cast<uint64_t *>(smem_raw);          // [total]
+    for (uint32_t i = threadIdx.x; i < total; i += blockDim.x)
+        ckey[i] = ((uint64_t)f2ord(a.cand_t[(size_t)q * a.cand_cap + i]) << 32) | a.cand_idx[(size_t)q * a.cand_cap + i];
     const uint32_t m = total < kprime ? total : kprime;   // candidates re-scored unconditionally
     __shared__ uint64_t rk[kRescoreCap];
     __shared__ uint32_t ri[kRescoreCap];
-    __shared__ uint32_t s_extra, s_fail, s_nout;
+    __shared__ uint32_t s_extra, s_fail, s_nout, s_hist[256], s_pick, s_fill;
+    if (threadIdx.x == 0) { s_extra = 0; s_fail = 0; s_fill = 0; }
+    uint64_t pivot = kKeySentinel;                          // m == total: everything is taken
+    if (m < total) {
+        uint64_t prefix = 0, pmask = 0;
+        uint32_t want = m;                                  // the want-th smallest among the keys matching the prefix
+        for (int shift = 56; shift >= 0; shift -= 8) {
+            s_hist[threadIdx.x] = 0;
+            __syncthreads();
+            for (uint32_t i = threadIdx.x; i < total; i += blockDim.x)
+                if ((ckey[i] & pmask) == prefix) atomicAdd(&s_hist[(uint32_t)(ckey[i] >> shift) & 255u], 1u);
+            __syncthreads();
+            if (warp == 0) {   // the bin in which the cumulative count reaches `want`: 8 bins per lane
+                uint32_t loc[8], sum = 0;
+#pragma unroll
+                for (int b = 0; b < 8; b++) { loc[b] = s_hist[lane * 8 + b]; sum += loc[b]; }
+                uint32_t incl = sum;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= (uint32_t)off) incl += o; }
+                const uint32_t excl = incl - sum;
+                if (excl < want && want <= incl) {
+                    uint32_t cum = excl;
+#pragma unroll
+                    for (int b = 0; b < 8; b++) {
+                        if (cum < want && want <= cum + loc[b]) { s_pick = (lane * 8 + b) | ((want - cum) << 8); }
+                        cum += loc[b];
+                    }
+                }
+            }
+            __syncthreads();
+            prefix |= (uint64_t)(s_pick & 255u) << shift;
+            pmask |= 0xFFull << shift;
+            want = s_pick >> 8;
+            __syncthreads();
+        }
+        pivot = prefix;
+    }
     const uint32_t R = next_pow2(m < 2 ? 2 : m);
-    for (uint32_t i = threadIdx.x; i < R; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = i < m ? idx[i] : kIdxSentinel; }
-    if (threadIdx.x == 0) { s_extra = 0; s_fail = 0; }
+    for (uint32_t i = threadIdx.x; i < R; i += blockDim.x) { rk[i] = kKeySentinel; ri[i] = kIdxSentinel; }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < total; i += blockDim.x)
+        if (ckey[i] <= pivot) ri[atomicAdd(&s_fill, 1u)] = (uint32_t)ckey[i];   // exactly m of them, in any order
     __syncthreads();
     // Exact fp32 re-score.  Each row is 4*dim bytes somewhere in HBM: the loop is written so that a warp has two
     // whole rows (2 x dim/128 independent 16-byte loads per lane) in flight at a time -- with scalar loads in a
@@ -638,9 +668,10 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
         }
         return have_k && !better(key, row, xkey, xidx);
     };
-    for (uint32_t c = m + threadIdx.x; c < total; c += blockDim.x) {
-        const uint32_t row = idx[c];
-        const float t = ord2f((uint32_t)keys[c]);
+    for (uint32_t c = threadIdx.x; c < total; c += blockDim.x) {
+        if (ckey[c] <= pivot) continue;                     // re-scored already
+        const uint32_t row = (uint32_t)ckey[c];
+        const float t = ord2f((uint32_t)(ckey[c] >> 32));
         bool excluded;
         const bool emb = (a.flags[row] & SPL_ROW_EMB) != 0;
         const float n2 = emb ? a.norm2[row] : 0.f, er2 = emb ? a.err2[row] : 0.f;
@@ -804,12 +835,6 @@ static cudaError_t launch_gemm(const CUtensorMap &mapQ, const CUtensorMap &mapE,
     return cudaLaunchKernelEx(&cfg, gemm_topk_kernel<true>, mapQ, mapE, a);
 }
 
-cudaError_t batch_scratch_init(BatchScratchLayout *L, unsigned char *scratch, cudaStream_t s) {
-    cudaError_t e = cudaMemsetAsync(scratch + L->exact_off, 0, 16, s);
-    if (e == cudaSuccess) L->exact_armed = true;
-    return e;
-}
-
 bool batch_supported(uint32_t dim, uint32_t k) { return dim % BK == 0 && dim >= BK && k >= 1 && k <= 128; }
 
 size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, BatchScratchLayout *L) {
@@ -824,13 +849,12 @@ size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, Batch
     L->ovf_off = take((size_t)nq_pad * 4);
     L->out_min_off = take((size_t)nq_pad * 4);
     L->out_tie_off = take((size_t)nq_pad * 4);
-    L->exact_off = take((size_t)(4 + 2 * kExactBoundBlocks) * 4);   // bound[2], ticket, pad, counts[blocks][2]
+    L->exact_off = take((size_t)(4 + 2 * kMaxSampledTiles) * 4);   // bound[2], pad[2], per-tile counts [sampled tiles][2]
     L->tile_min_off = take((size_t)tiles * nq_pad * 4);
     L->tile_min_row_off = take((size_t)tiles * nq_pad * 4);
     L->cand_t_off = take((size_t)nq_pad * kBatchCandCap * 4);
     L->cand_idx_off = take((size_t)nq_pad * kBatchCandCap * 4);
     L->nq_pad = nq_pad;
-    L->exact_armed = false;
     return off;
 }
 
@@ -870,12 +894,9 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     if ((e = cudaMemsetAsync(a.out_min, 0xFF, (size_t)a.nq_pad * 4, s))) return e;
     if ((e = cudaMemsetAsync(a.out_tie, 0, (size_t)a.nq_pad * 4, s))) return e;
 
-    {   // per-kind bounds for the rows that score exactly (see exact_bound_kernel); the ticket re-arms itself
+    {   // per-kind bounds for the rows that score exactly (exact_bound_block)
         uint32_t *ex = reinterpret_cast<uint32_t *>(scratch + L.exact_off);
-        a.exact_bound = ex;
-        if (!L.exact_armed) return cudaErrorInvalidValue;   // the ticket word must have been zeroed once (batch_scratch_init)
-        exact_bound_kernel<<<kExactBoundBlocks, 256, 0, s>>>(a, kprime, ex + 4, ex + 2, ex);
-        if ((e = cudaGetLastError())) return e;
+        a.exact_bound = ex; a.exact_bound_out = ex; a.tile_kinds = ex + 4;
     }
     const uint32_t tiles = (a.n + BN - 1) / BN;
     int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;
@@ -891,6 +912,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     if (sampled > tiles) sampled = tiles;
     if (sampled > kMaxSampledTiles) sampled = kMaxSampledTiles;   // threshold_kernel sorts the sample in shared memory
     a.pass = 1; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = sampled;
+    if ((e = cudaMemsetAsync(a.tile_kinds, 0, (size_t)sampled * 8, s))) return e;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
     // Which order statistic of the sampled tile minima becomes the bound: the list should hold about 16 k' entries, so
@@ -901,8 +923,8 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     uint32_t thr_rank = (uint32_t)(((uint64_t)16 * kprime * sampled + tiles - 1) / tiles);
     if (thr_rank > sampled / 2) thr_rank = sampled / 2;
     if (thr_rank < kprime) thr_rank = kprime;
-    threshold_kernel<<<a.nq, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, thr_rank, a.thr,
-                                                       a.thr_row);
+    threshold_kernel<<<a.nq + 1, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, thr_rank, a.thr,
+                                                           a.thr_row, a, kprime);
     if ((e = cudaGetLastError())) return e;
     // pass 2: every tile, append what beats the threshold
     a.pass = 2; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = tiles;
@@ -910,7 +932,7 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     const size_t sel_smem = (size_t)kBatchCandCap * 12;   // opted in by batch_prepare()
     select_rerank_kernel<<<a.nq, 256, sel_smem, s>>>(a, d_q32, k, kprime, d_out, out_stride, d_counts, overflow);
     if ((e = cudaGetLastError())) return e;
-    *launches = 6;
+    *launches = 5;
     return cudaSuccess;
 }
 

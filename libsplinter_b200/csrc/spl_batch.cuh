@@ -38,6 +38,8 @@ struct BatchArgs {
     uint32_t *out_min;            // [nq_pad]   f2ord of the best ordering value pass 2 kept OUT of the list as worse than thr
     uint32_t *out_tie;            // [nq_pad]   bit 0 / 1: exactly-scoring / ordinary rows tying with thr were cut off by row index
     const uint32_t *exact_bound;  // [2]        row index of the k'-th zero-vector / no-embedding candidate (kIdxSentinel: fewer)
+    uint32_t *exact_bound_out;    //            (the same words, written by exact_bound_block between the passes)
+    uint32_t *tile_kinds;         // [sampled tiles][2]  pass 1: candidates of either exactly-scoring kind per tile
     uint32_t *cand_cnt;           // [nq_pad]
     float *cand_t;                // [nq_pad][cand_cap]
     uint32_t *cand_idx;           // [nq_pad][cand_cap]
@@ -47,13 +49,11 @@ struct BatchArgs {
 struct BatchScratchLayout {
     size_t q16_off, thr_off, thr_row_off, cnt_off, ovf_off, out_min_off, out_tie_off, exact_off, tile_min_off, tile_min_row_off, cand_t_off, cand_idx_off;
     uint32_t nq_pad;
-    bool exact_armed;             // batch_scratch_init has zeroed the ticket word of exact_bound_kernel
 };
 
 cudaError_t batch_prepare();  // once per device
 bool batch_supported(uint32_t dim, uint32_t k);
 size_t batch_scratch_bytes(uint32_t n_rows, uint32_t nq_max, uint32_t dim, BatchScratchLayout *L);
-cudaError_t batch_scratch_init(BatchScratchLayout *L, unsigned char *scratch, cudaStream_t s);  // once, after allocating it
 // enqueues: query prep, sampling pass, thresholds, full pass, select + exact re-rank with its selection proof.
 // d_counts[q] = SPL_GPU_COUNT_UNANSWERED and bit 0 of the flag array returned in *d_overflow_out mark the queries
 // the bf16 pass could not answer (list overflow / unprovable selection); the other bits of a flag word hold the

@@ -1014,8 +1014,6 @@ static int ensure_batch_scratch(spl_gpu_ctx *c, uint32_t k) {
         const size_t bytes = batch_scratch_bytes((uint32_t)c->n, kBatchMaxQ, c->dim, &c->batch_layout);
         if ((rc = dev_alloc(c, &c->d_batch, bytes, false))) return rc;
         if ((rc = dev_alloc(c, &c->d_qbatch, (size_t)kBatchMaxQ * c->dim, false))) return rc;
-        CUDA_TRY(batch_scratch_init(&c->batch_layout, c->d_batch, c->stream));
-        CUDA_TRY(cudaStreamSynchronize(c->stream));   // the first batch may run on a caller's stream
     }
     const uint32_t need = kBatchMaxQ * k;
     if (c->bout_cap < need) {

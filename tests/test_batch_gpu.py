@@ -61,15 +61,15 @@ def test_batched_small_shapes_and_auto_mode():
         ref, rc = support.oracle_search_dense(q16, E, bloom, flags, k=10)
         for i in range(20):
             support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
-        # which path AUTO takes, seen through the launch counter (batched = 6 launches per call, scan = one per
+        # which path AUTO takes, seen through the launch counter (batched = 5 launches per call, scan = one per
         # group of up to 4 queries): unfiltered batches go to the tensor cores from 4 queries, masked ones from 16
         def launches(nq, **kw):
             before = m.launch_count()
             m.search(q16[:nq], 10, **kw)
             return m.launch_count() - before
-        assert launches(4) == 6 and launches(3) == 2                     # 3 queries: a 2-query and a 1-query scan
+        assert launches(4) == 5 and launches(3) == 2                     # 3 queries: a 2-query and a 1-query scan
         assert launches(4, bloom_mask=0x1) == 1 and launches(15, bloom_mask=0x1) == 5   # 4+4+4+2+1
-        assert launches(16, bloom_mask=0x1) == 6
+        assert launches(16, bloom_mask=0x1) == 5
         assert launches(20, max_distance=1.0) == 5                       # cosine order + distance threshold: 5 scans of 4
     finally:
         m.close()
@@ -190,11 +190,19 @@ def test_near_duplicates_do_not_fool_the_bf16_selection(dim, ndup, noise):
                 c0 = m.counters()
                 bad = _check(m, E, bloom, flags, q, k, order=order, bloom_mask=mask)   # oracle, ties within tolerance
                 c1 = m.counters()
-                # the three queries far from the crowd have no near-ties: the reference's indices exactly
-                assert not [i for i in bad if i >= 5], f"queries {bad} differ in their indices (order {order}, mask {mask})"
+                # the three queries far from the crowd: the reference's indices, except where two rows sit closer together
+                # than fp32 summation order can tell apart (1e-6, a twentieth of the suite's tolerance)
+                out, counts = _check.last
+                ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=k, order=order, bloom_mask=mask)
+                for i in [i for i in bad if i >= 5]:
+                    g, r = out[i][:counts[i]], ref[i][:rc[i]]
+                    prim = r["similarity"] if order == sg.ORDER_COSINE else r["distance"]
+                    pos = {int(ix): j for j, ix in enumerate(r["idx"])}
+                    for j in np.nonzero(g["slot_idx"] != r["idx"])[0]:
+                        other = pos.get(int(g["slot_idx"][j]), len(r) - 1)
+                        assert abs(float(prim[j]) - float(prim[other])) <= 1e-6, (i, j, order, mask)
                 # inside the crowd fp32 itself cannot separate every pair of rows the way the reference's sequential
                 # sums do (that is SPL_MODE_EXACT's job): there the bar is the fp32 scan's own answer, index for index
-                out, counts = _check.last
                 fast, fc = m.search(q, k, mode=sg.MODE_FAST, order=order, bloom_mask=mask)
                 for i in range(5):
                     assert counts[i] == fc[i]
