@@ -398,7 +398,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
                 if (++acc == kAcc) { acc = 0; aph ^= 1u; }
             }
             if (a.pass == 2 && qvalid) {
-                if (out_min < INFINITY) atomicMin(&a.out_min[q], f2ord(out_min));
+                if (out_min < INFINITY) atomicMax(&a.out_min[q], ~f2ord(out_min));   // stored inverted: 0 = nothing kept out
                 if (out_tie) atomicOr(&a.out_tie[q], out_tie);
             }
         }
@@ -447,14 +447,27 @@ __global__ void __launch_bounds__(256) qprep_kernel(const float *__restrict__ q,
 __device__ void exact_bound_block(const BatchArgs &a, uint32_t n_tiles, uint32_t kprime) {
     __shared__ uint32_t s_tile[2], s_res[2], s_w[8], s_run;
     const uint32_t need = a.mask ? SPL_ROW_ENUM : SPL_ROW_LIST;
-    if (threadIdx.x < 2) {
-        uint32_t cum = 0, tile = kIdxSentinel, res = 0;
-        for (uint32_t j = 0; j < n_tiles; j++) {    // (a few thousand L2 hits at worst; the k'-th is usually in the first tiles)
-            const uint32_t c = a.tile_kinds[2 * j + threadIdx.x];
-            if (cum + c >= kprime) { tile = j; res = kprime - cum; break; }
-            cum += c;
+    // thread i sums the counts of tiles [i*per, (i+1)*per); a block-wide scan of the 256 partial sums finds the thread
+    // whose range holds the k'-th row of a kind, and that thread walks its own range
+    __shared__ uint32_t s_part[2][256];
+    const uint32_t per = (n_tiles + blockDim.x - 1) / blockDim.x;
+    const uint32_t j0 = threadIdx.x * per, j1 = min(n_tiles, j0 + per);
+    uint32_t sum[2] = { 0, 0 };
+    for (uint32_t j = j0; j < j1; j++) { sum[0] += a.tile_kinds[2 * j]; sum[1] += a.tile_kinds[2 * j + 1]; }
+    s_part[0][threadIdx.x] = sum[0]; s_part[1][threadIdx.x] = sum[1];
+    if (threadIdx.x < 2) { s_tile[threadIdx.x] = kIdxSentinel; s_res[threadIdx.x] = 0; }
+    __syncthreads();
+    for (uint32_t kind = 0; kind < 2; kind++) {
+        uint32_t before = 0;
+        for (uint32_t i = 0; i < threadIdx.x; i++) before += s_part[kind][i];   // 256 shared-memory reads at most
+        if (before < kprime && kprime <= before + sum[kind]) {
+            uint32_t cum = before;
+            for (uint32_t j = j0; j < j1; j++) {
+                const uint32_t c = a.tile_kinds[2 * j + kind];
+                if (cum + c >= kprime) { s_tile[kind] = j; s_res[kind] = kprime - cum; break; }
+                cum += c;
+            }
         }
-        s_tile[threadIdx.x] = tile; s_res[threadIdx.x] = res;
     }
     __syncthreads();
     for (uint32_t kind = 1; kind <= 2; kind++) {
@@ -716,8 +729,8 @@ __global__ void __launch_bounds__(256) select_rerank_kernel(const BatchArgs a, c
             return lo > DkUp;
         };
         bool ok = true;
-        const uint32_t omin = a.out_min[q], tie = a.out_tie[q];
-        if (omin != 0xFFFFFFFFu) ok = bound_clears(ord2f(omin));
+        const uint32_t omin_inv = a.out_min[q], tie = a.out_tie[q];
+        if (omin_inv != 0u) ok = bound_clears(ord2f(~omin_inv));
         if (ok && (tie & 2u)) ok = bound_clears(a.thr[q]);
         if (ok && (tie & 1u)) {
             // exactly-scoring rows tying with the bound, all with a row index beyond thr_row: the best they can be is a
@@ -889,10 +902,6 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     cudaError_t e;
     qprep_kernel<<<a.nq_pad, 256, 0, s>>>(d_q32, a.nq, a.nq_pad, a.dim, q16);
     if ((e = cudaGetLastError())) return e;
-    if ((e = cudaMemsetAsync(a.cand_cnt, 0, (size_t)a.nq_pad * 4, s))) return e;
-    if ((e = cudaMemsetAsync(overflow, 0, (size_t)a.nq_pad * 4, s))) return e;
-    if ((e = cudaMemsetAsync(a.out_min, 0xFF, (size_t)a.nq_pad * 4, s))) return e;
-    if ((e = cudaMemsetAsync(a.out_tie, 0, (size_t)a.nq_pad * 4, s))) return e;
 
     {   // per-kind bounds for the rows that score exactly (exact_bound_block)
         uint32_t *ex = reinterpret_cast<uint32_t *>(scratch + L.exact_off);
@@ -902,27 +911,32 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     int grid = sm_count / (int)a.n_qtiles * (int)a.n_qtiles;
     if (grid < (int)a.n_qtiles) grid = (int)a.n_qtiles;
     if (pair) grid &= ~1;
-    // pass 1: a PREFIX of the tiles (all of them when the shard is small) -> per-tile minima -> thresholds.
-    // With a 1/f sample the expected survivors of pass 2 are ~ f * k'; a prefix (not a strided sample) keeps
-    // that true for ties on t as well, because the bound is the pair (t, row).
-    uint32_t frac = 1024u / kprime;
-    if (frac > 16) frac = 16;
-    uint32_t sampled = tiles / (frac ? frac : 1);
-    if (sampled < 4 * kprime) sampled = 4 * kprime;
+    // pass 1: a PREFIX of the tiles (1/64 of them, at least 64, all when the shard is small) -> per-tile minima ->
+    // thresholds.  A prefix (not a strided sample) keeps the estimate below true for ties on t as well, because the
+    // bound is the pair (t, row).  The sample only has to place the bound roughly: whatever it yields, the selection
+    // proof in select_rerank_kernel decides whether the list it produced can be trusted.
+    uint32_t sampled = tiles / 64;
+    if (sampled < 64) sampled = 64;
     if (sampled > tiles) sampled = tiles;
     if (sampled > kMaxSampledTiles) sampled = kMaxSampledTiles;   // threshold_kernel sorts the sample in shared memory
     a.pass = 1; a.tile_first = 0; a.tile_stride = 1; a.n_tiles = sampled;
-    if ((e = cudaMemsetAsync(a.tile_kinds, 0, (size_t)sampled * 8, s))) return e;
+    // one fill for everything that must start at zero: candidate counts, overflow flags, out_min (stored inverted), tie
+    // flags, the exact-kind bounds and per-tile counts -- laid out back to back by batch_scratch_bytes
+    if ((e = cudaMemsetAsync(scratch + L.cnt_off, 0, L.exact_off + (size_t)(4 + 2 * sampled) * 4 - L.cnt_off, s))) return e;
     if ((e = launch_gemm(mapQ, mapE, a, pair, grid, s))) return e;
     const uint32_t P = next_pow2(sampled < 2 ? 2 : sampled);
     // Which order statistic of the sampled tile minima becomes the bound: the list should hold about 16 k' entries, so
     // that a crowd of near-ties around the k-th score is IN the list (the selection proof can then re-score it) and
     // the rows left out are far enough from the k-th for the proof's bound to clear them.  With a 1/f sample the
     // k'-th smallest minimum already sits near rank f k' of the shard; a small shard that is sampled whole needs a
-    // later one (but no later than half of its tiles: one candidate per tile is all the minima can vouch for).
+    // later one (but no later than half of its tiles: one candidate per tile is all the minima can vouch for).  The order
+    // statistic may be smaller than k: then the minima alone do not guarantee k rows under the bound, but in expectation
+    // ~16 k' rows are, and a list that did come out short fails the proof and goes to the fp32 scan.
     uint32_t thr_rank = (uint32_t)(((uint64_t)16 * kprime * sampled + tiles - 1) / tiles);
-    if (thr_rank > sampled / 2) thr_rank = sampled / 2;
-    if (thr_rank < kprime) thr_rank = kprime;
+    const uint32_t rank_hi = tiles <= 64 ? sampled : sampled / 2;
+    if (thr_rank > rank_hi) thr_rank = rank_hi;
+    if (thr_rank < 8) thr_rank = 8;
+    if (a.n <= kBatchCandCap) thr_rank = sampled + 1;   // the whole shard fits the list: no bound (+inf), every candidate is listed
     threshold_kernel<<<a.nq + 1, 256, (size_t)P * 12, s>>>(a.tile_min, a.tile_min_row, sampled, a.nq, a.nq_pad, thr_rank, a.thr,
                                                            a.thr_row, a, kprime);
     if ((e = cudaGetLastError())) return e;
