@@ -157,7 +157,10 @@ def workload_config(n_gpus):
         return {"workload": "C2: 2^20 slots x 768-d fp32, single-query cosine top-10, bloom-label pre-filter mask 0x3 "
                             "(12.2% of slots pass); mirror resident in HBM (3.2 GB > 126 MB L2, no flush needed)",
                 "slots": C2_ROWS, "dim": DIM, "k": C2_K, "bloom_mask": "0x3", "parallelism": "1 GPU",
-                "l2_policy": "inputs larger than L2"}
+                "l2_policy": "inputs larger than L2",
+                "pipelining": "`value`: a query loop on one stream, searches flagged SPL_SEARCH_PIPELINED (a scan may start while "
+                              "the previous one merges its per-SM lists; results in stream order); `latency_us` and `e2e`: one "
+                              "search at a time, nothing overlapped"}
     return {"workload": f"C4: 2^26 slots x 768-d fp32 sharded by slot range over {n_gpus} GPUs, single-query cosine "
                         "top-100, per-GPU top-k all-gathered over NCCL + device merge",
             "slots": C4_ROWS, "dim": DIM, "k": C4_K, "bloom_mask": "0", "parallelism": f"slot-range shards x{n_gpus}",
@@ -255,7 +258,8 @@ def run_ours(args):
         return int((((flags_h & need) != 0) & ((bloom_h & np.uint64(mask)) == np.uint64(mask))).sum())
 
     def device_step(i, mask, qsrc=None):
-        p = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask)
+        # a query loop: each search directly follows another search of this context on this stream
+        p = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask, flags=sg.SEARCH_PIPELINED)
         qv = qsrc if qsrc is not None else q_dev[i % N_QUERIES]
         if world > 1:
             sharded.enqueue(p, qv)      # (fp32 scan: always answers, no re-issue to wait for)

@@ -85,8 +85,17 @@ typedef struct spl_gpu_search_params {
     float    max_distance;   /* --distance;   <= 0 disables (_search.c:399) */
     uint32_t exclude_slot;   /* slot of the caller's scratch key (_search.c:367); SPL_NO_SLOT = none.
                                 Index is GLOBAL (store slot index), like every index in this API. */
-    uint32_t reserved;
+    uint32_t flags;          /* SPL_SEARCH_* */
 } spl_gpu_search_params;
+
+/* spl_gpu_search_device only: this search directly follows another search of the SAME context on the SAME stream (a
+ * query loop), and whatever else the caller may have enqueued on that stream in between neither writes this search's
+ * query buffer nor was itself launched to overlap its predecessor.  The scan may then begin while the previous scan
+ * is still merging its per-SM lists (a few microseconds during which all but one SM would idle).  Results are
+ * unchanged and still land in stream order -- consecutive searches may share their output buffers.  Without the flag
+ * every search waits for everything before it on the stream, as any kernel does.  (Within one call the queries of a
+ * batch always overlap this way.) */
+#define SPL_SEARCH_PIPELINED 0x1u
 
 /* One hit.  Mirrors search_result_t (_search.c:26-35) with the key replaced by its slot index
  * (slot_ptr - S); key / val_len / type are resolved from the store by the host caller. */

@@ -31,6 +31,7 @@ ROW_LIST, ROW_ENUM, ROW_EMB = 0x1, 0x2, 0x4
 NO_SLOT = 0xFFFFFFFF
 KMAX_FUSED = 256
 COUNT_UNANSWERED = 0xFFFFFFFF
+SEARCH_PIPELINED = 0x1
 
 
 class Opts(C.Structure):
@@ -42,7 +43,7 @@ class SearchParams(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("nq", C.c_uint32), ("dim", C.c_uint32), ("k", C.c_uint32),
                 ("order", C.c_uint32), ("mode", C.c_uint32), ("bloom_mask", C.c_uint64),
                 ("min_similarity", C.c_float), ("max_distance", C.c_float), ("exclude_slot", C.c_uint32),
-                ("reserved", C.c_uint32)]
+                ("flags", C.c_uint32)]
 
 
 class SyncStats(C.Structure):
@@ -253,9 +254,9 @@ class Mirror:
         return E, bloom, flags, epoch
 
     def params(self, nq, k, order=ORDER_COSINE, mode=MODE_AUTO, bloom_mask=0, min_similarity=0.0,
-               max_distance=0.0, exclude_slot=NO_SLOT) -> SearchParams:
+               max_distance=0.0, exclude_slot=NO_SLOT, flags=0) -> SearchParams:
         return SearchParams(C.sizeof(SearchParams), nq, self._dim, k, order, mode, bloom_mask,
-                            min_similarity, max_distance, exclude_slot, 0)
+                            min_similarity, max_distance, exclude_slot, flags)
 
     def search(self, q, k, out_stride=None, **kw):
         """Host-buffer search.  Returns (results[nq, stride] structured array, counts[nq])."""

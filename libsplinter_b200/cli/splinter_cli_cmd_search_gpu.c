@@ -10,7 +10,7 @@
  *
  * and is compiled against the reference's own splinter_cli.h / splinter.h / 3rdparty/grawk.h.  Build the
  * reference CLI with this file in place of splinter_cli_cmd_search.c and link -lsplinter_gpu: nothing else
- * in the reference changes (oracle/Makefile builds exactly that as _ref/splinterctl_gpu for the tests).
+ * in the reference changes (oracle/Makefile builds exactly that as _ref/gpu/splinterctl for the tests).
  *
  * What stays on the host, with the reference's behaviour: flag parsing (_search.c:170-215), reading the
  * query text (:242-275), the scratch-key handshake with the embedding daemon (:301-327), the key regex
@@ -173,14 +173,17 @@ int cmd_search(int argc, char *argv[]) {
         query_text = query_buffer;
     }
 
+    /* Bring the mirror up to date BEFORE the handshake: splinter_poll only sees an answer that arrives after it
+     * was called (splinter.c:479-516), so nothing slow -- a first attach creates the CUDA context and uploads the
+     * whole store -- may sit between the bump below and the poll. */
+    spl_gpu_ctx *gpu = gpu_for_current_store();
+
     /* ---- query-vector handshake with the embedding daemon (_search.c:301-327), unchanged ---- */
     splinter_set(scratch_key, query_text, query_buffer ? query_len : strlen(query_text));
     splinter_set_named_type(scratch_key, SPL_SLOT_TYPE_VARTEXT);
     splinter_set_label(scratch_key, 1ULL);
     splinter_bump_slot(scratch_key);
     scratch_written = 1;
-    /* bring the mirror up to date while the daemon computes the query vector: attach / sync overlap the wait */
-    spl_gpu_ctx *gpu = gpu_for_current_store();
     const int poll_rc = splinter_poll(scratch_key, 2000);
     float query_vec[SPLINTER_EMBED_DIM];
     memset(query_vec, 0, sizeof query_vec);

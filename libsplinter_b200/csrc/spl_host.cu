@@ -109,8 +109,13 @@ struct spl_gpu_ctx {
     uint32_t stage_rows = 0, stage_meta = 0;
     // search scratch
     int scan_grid = 0;
-    Cand *d_cands = nullptr;
-    uint32_t *d_counters = nullptr;
+    // Two scratch sets (per-CTA candidate lists + counters) used by alternate scan launches, so that a scan may start
+    // while its predecessor is still merging (see scan_tma_kernel); d_cands / d_counters = set 0.
+    Cand *d_cands = nullptr, *d_cands_set[2] = { nullptr, nullptr };
+    uint32_t *d_counters = nullptr, *d_counters_set[2] = { nullptr, nullptr };
+    uint32_t scan_set = 0;                 // set the NEXT scan launch takes
+    cudaStream_t last_tma_stream = nullptr;  // stream of the most recent launch if that was a TMA scan, else null
+    bool last_was_tma = false;
     float *d_q = nullptr, *h_q = nullptr;
     spl_gpu_result *d_out = nullptr, *h_out = nullptr;
     uint32_t *d_count = nullptr, *h_count = nullptr;
@@ -156,6 +161,7 @@ struct spl_gpu_ctx {
     std::atomic<uint64_t> launches{0};
     bool force_ldg = false;
     bool no_multi = false;  // developer knob SPL_GPU_SCAN_MULTI=0: one query per launch even for small batches
+    bool no_overlap = false;  // developer knob SPL_GPU_SCAN_OVERLAP=0: never let a scan start during its predecessor's tail
     unsigned long long *d_dbg = nullptr;  // SPL_GPU_DEBUG_TIMELINE=1: per-CTA timestamps of the last scan
     bool timing = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -192,6 +198,8 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     c->force_ldg = impl && strcmp(impl, "ldg") == 0;
     const char *multi = getenv("SPL_GPU_SCAN_MULTI");
     c->no_multi = multi && strcmp(multi, "0") == 0;
+    const char *ovl = getenv("SPL_GPU_SCAN_OVERLAP");
+    c->no_overlap = ovl && strcmp(ovl, "0") == 0;
     if (getenv("SPL_GPU_DEBUG_TIMELINE")) {
         CUDA_TRY(cudaMalloc((void **)&c->d_dbg, 1024 * 8 * sizeof(unsigned long long)));
         CUDA_TRY(cudaMemset(c->d_dbg, 0, 1024 * 8 * sizeof(unsigned long long)));
@@ -226,8 +234,10 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     // search scratch
     c->scan_grid = c->sm_count * scan_fast_ctas_per_sm(c->dim, 0);
     // one k-entry list per CTA and query: up to 4 queries x 256 entries (small batches) per launch
-    if ((rc = dev_alloc(c, &c->d_cands, (size_t)c->scan_grid * SPL_GPU_KMAX_FUSED * 4, false))) return rc;
-    if ((rc = dev_alloc(c, &c->d_counters, 16, true))) return rc;   // chunk, ticket, 4 survivor counts, 3 more tickets
+    if ((rc = dev_alloc(c, &c->d_cands, (size_t)c->scan_grid * SPL_GPU_KMAX_FUSED * 4 * 2, false))) return rc;
+    if ((rc = dev_alloc(c, &c->d_counters, 32, true))) return rc;   // per set: chunk, ticket, 4 survivor counts, 3 more tickets
+    c->d_cands_set[0] = c->d_cands; c->d_cands_set[1] = c->d_cands + (size_t)c->scan_grid * SPL_GPU_KMAX_FUSED * 4;
+    c->d_counters_set[0] = c->d_counters; c->d_counters_set[1] = c->d_counters + 16;
     c->q_cap = 64;
     c->out_cap = 64 * SPL_GPU_KMAX_FUSED;
     if ((rc = dev_alloc(c, &c->d_q, (size_t)c->q_cap * c->dim, false))) return rc;
@@ -502,8 +512,9 @@ static int order_before_search(spl_gpu_ctx *c, cudaStream_t s) {
     if (s != c->stream && c->flush_recorded) CUDA_TRY(cudaStreamWaitEvent(s, c->ev_flush, 0));
     if (c->search_recorded && c->search_stream != s) CUDA_TRY(cudaStreamWaitEvent(s, c->ev_search, 0));
     if (c->counters_dirty) {
-        CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(uint32_t), s));
+        CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, 32 * sizeof(uint32_t), s));
         c->counters_dirty = false;
+        c->last_was_tma = false;
     }
     return 0;
 }
@@ -519,6 +530,7 @@ static int flush_buf(spl_gpu_ctx *c, StageBuf &b, bool rows, SyncCounters &sc) {
     if (b.n == 0) return 0;
     std::lock_guard<std::mutex> lk(c->mu);
     const size_t row_bytes = (size_t)c->dim * 4;
+    c->last_was_tma = false;
     if (order_before_update(c)) return -1;
     if (rows) {
         CUDA_TRY(cudaMemcpyAsync(b.d_rows, b.h_rows, (size_t)b.n * row_bytes, cudaMemcpyHostToDevice, c->stream));
@@ -902,7 +914,7 @@ static void fill_args(const spl_gpu_ctx *c, const spl_gpu_search_params *p, Scan
     if (p->exclude_slot != SPL_NO_SLOT && p->exclude_slot >= c->slot_begin && p->exclude_slot < c->slot_begin + c->n)
         a.exclude = (uint32_t)(p->exclude_slot - c->slot_begin);
     a.row0 = c->slot_begin;
-    a.cta_cands = c->d_cands; a.counters = c->d_counters;
+    a.cta_cands = c->d_cands_set[c->scan_set]; a.counters = c->d_counters_set[c->scan_set];
     a.dbg = c->d_dbg;
 }
 
@@ -931,8 +943,20 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         a.out = d_out + (size_t)qi * out_stride;
         a.out_count = d_counts + (size_t)qi * count_stride;
         a.total = d_totals ? d_totals + qi : nullptr;
-        if (tma) CUDA_TRY(launch_scan_tma(a, c->sm_count, s));
-        else CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
+        // alternate scratch sets from launch to launch; a TMA scan that directly follows another TMA scan of this
+        // context on the same stream may start during its predecessor's tail: always inside one call, across calls
+        // only when the caller says nothing else sits between them (SPL_SEARCH_PIPELINED)
+        a.cta_cands = c->d_cands_set[c->scan_set]; a.counters = c->d_counters_set[c->scan_set];
+        c->scan_set ^= 1u;
+        if (tma) {
+            a.overlap_prev = c->last_was_tma && c->last_tma_stream == s && !c->no_overlap &&
+                             (qi > 0 || (p->flags & SPL_SEARCH_PIPELINED)) ? 1u : 0u;
+            CUDA_TRY(launch_scan_tma(a, c->sm_count, s));
+            c->last_was_tma = true; c->last_tma_stream = s;
+        } else {
+            CUDA_TRY(launch_scan_fast(a, c->scan_grid, s));
+            c->last_was_tma = false;
+        }
         c->launches++;
         qi += g;
     }
@@ -999,6 +1023,7 @@ static int enqueue_exact(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         CUDA_TRY(launch_exact_rescore(a, s));
         c->launches++;
     }
+    c->last_was_tma = false;
     return 0;
 }
 
@@ -1066,6 +1091,7 @@ static int enqueue_batch(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         b.exclude = (uint32_t)(p->exclude_slot - c->slot_begin);
     b.row0 = c->slot_begin;
     uint32_t launches = 0;
+    c->last_was_tma = false;
     CUDA_TRY(batch_search(b, c->batch_layout, c->d_batch, d_q, p->k, c->sm_count, d_out, out_stride, d_counts, d_overflow,
                           &launches, s));
     c->launches += launches;
@@ -1149,6 +1175,7 @@ static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const
     a.out = c->d_big_out;
     a.out_count = c->d_count;
     a.k = 0;
+    c->last_was_tma = false;
     if (exact) CUDA_TRY(launch_exact_all(a, c->sm_count, c->stream));
     else CUDA_TRY(launch_scan_fast(a, c->scan_grid, c->stream));
     CUDA_TRY(launch_sortall(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, cap, c->stream));
@@ -1333,6 +1360,7 @@ extern "C" int spl_gpu_merge_topk_device(spl_gpu_ctx *c, const spl_gpu_result *d
     if (k == 0 || k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "merge needs k in 1..%u", SPL_GPU_KMAX_FUSED);
     if (order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order");
     cudaSetDevice(c->device);
+    { std::lock_guard<std::mutex> lk(c->mu); c->last_was_tma = false; }
     CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, 1, list_stride, order, k, d_out, k, d_out_count,
                                   stream ? (cudaStream_t)stream : c->stream));
     c->launches++;
@@ -1347,6 +1375,7 @@ extern "C" int spl_gpu_merge_topk_batch_device(spl_gpu_ctx *c, const spl_gpu_res
     if (order > SPL_ORDER_L2) return fail(-2, EINVAL, "unknown order");
     if (nq == 0 || out_stride < k) return fail(-2, EINVAL, "merge needs nq >= 1 and out_stride >= k");
     cudaSetDevice(c->device);
+    { std::lock_guard<std::mutex> lk(c->mu); c->last_was_tma = false; }
     CUDA_TRY(launch_merge_results(d_lists, d_counts, nlists, nq, list_stride, order, k, d_out, out_stride, d_out_counts,
                                   stream ? (cudaStream_t)stream : c->stream));
     c->launches++;
@@ -1363,6 +1392,7 @@ extern "C" int spl_gpu_merge_topk_packed_device(spl_gpu_ctx *c, const void *d_pa
     const size_t block = SPL_GPU_PACKED_BLOCK_BYTES(nq, list_stride);
     const unsigned char *base = static_cast<const unsigned char *>(d_packed);
     cudaSetDevice(c->device);
+    { std::lock_guard<std::mutex> lk(c->mu); c->last_was_tma = false; }
     CUDA_TRY(launch_merge_results(reinterpret_cast<const spl_gpu_result *>(base),
                                   reinterpret_cast<const uint32_t *>(base + SPL_GPU_PACKED_COUNTS_OFFSET(nq, list_stride)), nlists, nq,
                                   list_stride, order, k, d_out, out_stride, d_out_counts,

@@ -519,6 +519,21 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         if (a.total && (lane % (4 * TB)) == 0 && nsurv) atomicAdd(&a.counters[2 + my_q], nsurv);
     }
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 2] = gtime();
+    // ---- back-to-back scans (programmatic dependent launch) ---------------------------------------------------------
+    // What is left of this launch after the scan loop is a few microseconds of merging, most of it in ONE CTA while
+    // the other SMs idle.  If the next launch on the stream is another scan (the host says so with the launch
+    // attribute), let it begin now: its CTAs take the SMs as this launch's CTAs leave.  Two rules keep that safe.
+    //  * Consecutive launches use alternating scratch sets (work counter, tickets, per-CTA lists), so launch i+1
+    //    shares nothing with launch i but the read-only mirror.  Launch i+2 reuses launch i's set: by then launch i
+    //    must be over, and it is, because every CTA WAITS for the launch before its own to have completed (and
+    //    flushed) before it gives the go-ahead -- launch i+2 cannot start unless all of launch i+1 have done so.
+    //  * The same wait orders the result writes of consecutive launches (a caller may hand every query the same
+    //    output buffer).
+    // Without the launch attribute both instructions do nothing.
+    if (warp == kConsumers && lane == 0) {   // a producer lane: done as soon as the sequence is closed
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    }
     // the row ring is idle now: it becomes the workspace of the final cross-CTA merge
     uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
     uint64_t *ws_keys = reinterpret_cast<uint64_t *>(smem + L.rows_off);
@@ -549,8 +564,23 @@ bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq) {
 template <int V, int NQ>
 static cudaError_t launch_v(const ScanArgs &a, int grid, cudaStream_t stream) {
     const TmaLayout L = tma_layout(a.dim, a.k, NQ);
-    scan_tma_kernel<V, NQ><<<grid, kTmaThreads, L.total, stream>>>(a);
-    return cudaGetLastError();
+    if (!a.overlap_prev) {
+        scan_tma_kernel<V, NQ><<<grid, kTmaThreads, L.total, stream>>>(a);
+        return cudaGetLastError();
+    }
+    // may begin while the previous kernel on the stream (another scan: the caller of this function vouches for it) is
+    // still in its tail; see the protocol in the kernel
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kTmaThreads);
+    cfg.dynamicSmemBytes = L.total;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, scan_tma_kernel<V, NQ>, a);
 }
 
 template <int V>

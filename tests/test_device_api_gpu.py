@@ -135,3 +135,41 @@ def test_batched_merge_of_gathered_shard_blocks():
     finally:
         for m in mirrors:
             m.close()
+
+
+def test_pipelined_query_loop_returns_what_one_at_a_time_returns():
+    """SPL_SEARCH_PIPELINED lets a scan start during the previous scan's merge tail (alternating scratch sets, results
+    written in stream order).  200 different queries back to back, each into its own output area, then 50 more all into
+    ONE area: the bytes must be those of the unflagged loop, and the shared area must hold the LAST query's answer."""
+    n, dim, k, nq = 300_000, 768, 10, 200
+    stream = torch.cuda.Stream()
+    rng = np.random.default_rng(8)
+    q = rng.standard_normal((nq, dim)).astype(np.float32)
+    with sg.Mirror.open_dense(n, dim) as m:
+        m.fill_synthetic(1234, 99)
+        dq = torch.from_numpy(q).cuda()
+        outs = {}
+        for flags in (0, sg.SEARCH_PIPELINED):
+            out = torch.zeros((nq, k, 32), dtype=torch.uint8, device="cuda")
+            cnt = torch.zeros(nq, dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            for mask in (0x3, 0x7, 0):
+                p = m.params(1, k, bloom_mask=mask, mode=sg.MODE_FAST, flags=flags)
+                with torch.cuda.stream(stream):
+                    for i in range(nq):
+                        m.search_device(p, dq[i].data_ptr(), out[i].data_ptr(), k, cnt[i:].data_ptr(), stream.cuda_stream)
+                stream.synchronize()
+                outs[(flags, mask)] = (out.cpu().numpy().copy(), cnt.cpu().numpy().copy())
+        for mask in (0x3, 0x7, 0):
+            a, b = outs[(0, mask)], outs[(sg.SEARCH_PIPELINED, mask)]
+            assert np.array_equal(a[1], b[1]) and np.all(a[1] == k)
+            assert a[0].tobytes() == b[0].tobytes()
+        # one shared output area: stream order decides who writes last
+        one = torch.zeros((k, 32), dtype=torch.uint8, device="cuda")
+        c1 = torch.zeros(1, dtype=torch.int32, device="cuda")
+        p = m.params(1, k, bloom_mask=0x7, mode=sg.MODE_FAST, flags=sg.SEARCH_PIPELINED)
+        with torch.cuda.stream(stream):
+            for i in range(50):
+                m.search_device(p, dq[i].data_ptr(), one.data_ptr(), k, c1.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        assert one.cpu().numpy().tobytes() == outs[(0, 0x7)][0][49].tobytes()
