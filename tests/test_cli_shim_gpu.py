@@ -24,10 +24,9 @@ CASES = [["--limit", "10"], ["--json", "--limit", "7"], ["--bloom", "3", "--json
          ["--json"]]
 
 
-@pytest.fixture()
-def store(tmp_path):
+def _make_store(name):
+    """700 keys (two key families, most with an embedding, random labels) through the reference's own library"""
     ref = support.ref_store()
-    name = f"/splb200_cli_{os.getpid()}"
     path = "/dev/shm" + name
     if os.path.exists(path):
         os.unlink(path)
@@ -43,11 +42,18 @@ def store(tmp_path):
         if m:
             ref.splinter_set_label(key, m)
     ref.splinter_close()
+    return rng
+
+
+@pytest.fixture()
+def store(tmp_path):
+    name = f"/splb200_cli_{os.getpid()}"
+    rng = _make_store(name)
     qfile = tmp_path / "q.f32"
     rng.standard_normal(DIM).astype(np.float32).tofile(qfile)
     yield name, str(qfile)
-    if os.path.exists(path):
-        os.unlink(path)
+    if os.path.exists("/dev/shm" + name):
+        os.unlink("/dev/shm" + name)
 
 
 def _one_shot(binary, name, qfile, flags, pre=("--use",)):
@@ -94,7 +100,7 @@ def test_repl_session_keeps_the_mirror_between_queries(store):
         stub.wait(timeout=60)
         assert r.returncode == 0, r.stderr
         outs.append(r.stdout)
-        subprocess.run([str(STOCK), "--use", name, "unset", "zzz_new_key"], capture_output=True)
+        _make_store(name)   # the session wrote to the store: give the other binary the same starting point
     assert outs[0] == outs[1]
     assert outs[0].count('"results"') == 3 and "zzz_new_key" in outs[0]
 
