@@ -294,6 +294,31 @@ int spl_gpu_merge_topk_packed_device(spl_gpu_ctx *ctx, const void *d_packed, uin
                                      uint32_t list_stride, uint32_t order, uint32_t k, spl_gpu_result *d_out,
                                      uint32_t out_stride, uint32_t *d_out_counts, void *stream);
 
+/* ---- several GPUs behind one call ---------------------------------------------------------------------------- */
+
+/* One process, one context per GPU, each mirroring a contiguous slot range [i*ceil(N/G), ...) of the same store
+ * (the reference itself is single-host, single-address-space: splinter.h:542-544).  A search runs the
+ * per-GPU scans side by side, pulls each GPU's packed top-k block onto the first device with one peer copy, merges
+ * there with the reference's comparator + global slot index, and returns the merged records: the same bytes a single
+ * context over the whole store returns.  Queries a shard could not answer in the requested mode
+ * (SPL_GPU_COUNT_UNANSWERED) are re-issued on the fp32 scan by the call itself.  devices[] = CUDA ordinals (NULL =
+ * 0..n_devices-1; an ordinal may repeat: several shards on one GPU).  k in 1..SPL_GPU_KMAX_FUSED. */
+typedef struct spl_gpu_group spl_gpu_group;
+spl_gpu_group *spl_gpu_group_attach(const char *name_or_path, uint32_t n_devices, const int32_t *devices,
+                                    const spl_gpu_opts *opts /* device, slot_begin, slot_count are set per shard */);
+spl_gpu_group *spl_gpu_group_open_dense(uint64_t n_rows, uint32_t dim, uint32_t n_devices, const int32_t *devices,
+                                        const spl_gpu_opts *opts);
+void     spl_gpu_group_detach(spl_gpu_group *g);
+uint32_t spl_gpu_group_size(const spl_gpu_group *g);
+spl_gpu_ctx *spl_gpu_group_member(spl_gpu_group *g, uint32_t i);   /* shard i's context (info, counters, dense upload) */
+/* all shards sweep their slot ranges at once; *total (nullable) = sums, and the slowest shard's times */
+int spl_gpu_group_sync(spl_gpu_group *g, spl_gpu_sync_stats *total);
+int spl_gpu_group_fill_synthetic(spl_gpu_group *g, uint64_t seed_corpus, uint64_t seed_bloom);
+/* host-buffer search over all shards; arguments as spl_gpu_search */
+int spl_gpu_group_search(spl_gpu_group *g, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
+                         uint32_t out_stride, uint32_t *counts);
+uint64_t spl_gpu_group_reissued(const spl_gpu_group *g);   /* queries re-issued on the fp32 scan so far */
+
 /* Allocation-free variant of the fused single-query scan.  (No counterpart in the reference; it
  * exists only because of how GPU memory is managed.)
  *

@@ -22,6 +22,8 @@ ABI_SYMBOLS = [
     "spl_gpu_read_mirror", "spl_gpu_search", "spl_gpu_search_device", "spl_gpu_merge_topk_device", "spl_gpu_merge_topk_batch_device",
     "spl_gpu_launch_count", "spl_gpu_set_timing", "spl_gpu_last_scan_ms", "spl_gpu_scan_noalloc", "spl_gpu_slot_meta", "spl_gpu_last_totals",
     "spl_gpu_get_counters", "spl_gpu_find_key", "spl_gpu_merge_topk_packed_device",
+    "spl_gpu_group_attach", "spl_gpu_group_open_dense", "spl_gpu_group_detach", "spl_gpu_group_size", "spl_gpu_group_member",
+    "spl_gpu_group_sync", "spl_gpu_group_fill_synthetic", "spl_gpu_group_search", "spl_gpu_group_reissued",
 ]
 
 ORDER_COSINE, ORDER_L2 = 0, 1
@@ -117,6 +119,24 @@ def load() -> C.CDLL:
     lib.spl_gpu_merge_topk_batch_device.argtypes = [vp, vp, vp, u32, u32, u32, u32, u32, vp, u32, vp, vp]
     lib.spl_gpu_merge_topk_packed_device.restype = C.c_int
     lib.spl_gpu_merge_topk_packed_device.argtypes = [vp, vp, u32, u32, u32, u32, u32, vp, u32, vp, vp]
+    lib.spl_gpu_group_attach.restype = vp
+    lib.spl_gpu_group_attach.argtypes = [C.c_char_p, u32, C.POINTER(C.c_int32), C.POINTER(Opts)]
+    lib.spl_gpu_group_open_dense.restype = vp
+    lib.spl_gpu_group_open_dense.argtypes = [u64, u32, u32, C.POINTER(C.c_int32), C.POINTER(Opts)]
+    lib.spl_gpu_group_detach.restype = None
+    lib.spl_gpu_group_detach.argtypes = [vp]
+    lib.spl_gpu_group_size.restype = u32
+    lib.spl_gpu_group_size.argtypes = [vp]
+    lib.spl_gpu_group_member.restype = vp
+    lib.spl_gpu_group_member.argtypes = [vp, u32]
+    lib.spl_gpu_group_sync.restype = C.c_int
+    lib.spl_gpu_group_sync.argtypes = [vp, C.POINTER(SyncStats)]
+    lib.spl_gpu_group_fill_synthetic.restype = C.c_int
+    lib.spl_gpu_group_fill_synthetic.argtypes = [vp, u64, u64]
+    lib.spl_gpu_group_search.restype = C.c_int
+    lib.spl_gpu_group_search.argtypes = [vp, C.POINTER(SearchParams), vp, vp, u32, vp]
+    lib.spl_gpu_group_reissued.restype = u64
+    lib.spl_gpu_group_reissued.argtypes = [vp]
     lib.spl_gpu_scan_noalloc.restype = C.c_int
     lib.spl_gpu_scan_noalloc.argtypes = [vp, vp, vp, vp, u64, u64, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_slot_meta.restype = C.c_int
@@ -312,3 +332,78 @@ class Mirror:
 
     def last_scan_ms(self) -> float:
         return float(self._lib.spl_gpu_last_scan_ms(self._h))
+
+
+class Group:
+    """Several GPUs behind one call (spl_gpu_group_*): one context per device over contiguous slot ranges."""
+
+    def __init__(self, handle, dim):
+        self._lib = load()
+        if not handle:
+            raise SplinterGpuError(self._lib.spl_gpu_last_error().decode() or "group attach failed")
+        self._h = C.c_void_p(handle)
+        self._dim = dim
+
+    @staticmethod
+    def _devs(devices):
+        return (C.c_int32 * len(devices))(*devices)
+
+    @classmethod
+    def attach(cls, name_or_path: str, devices, dim=768, **kw):
+        o = _opts(**kw)
+        return cls(load().spl_gpu_group_attach(name_or_path.encode(), len(devices), cls._devs(devices), C.byref(o)), dim)
+
+    @classmethod
+    def open_dense(cls, n_rows: int, dim: int, devices, **kw):
+        o = _opts(**kw)
+        return cls(load().spl_gpu_group_open_dense(n_rows, dim, len(devices), cls._devs(devices), C.byref(o)), dim)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise SplinterGpuError(f"rc={rc} errno={C.get_errno()}: {self._lib.spl_gpu_last_error().decode()}")
+
+    def close(self):
+        if self._h:
+            self._lib.spl_gpu_group_detach(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def size(self) -> int:
+        return int(self._lib.spl_gpu_group_size(self._h))
+
+    def member(self, i) -> "Mirror":
+        """a NON-owning view of shard i's context (do not close it)"""
+        m = Mirror.__new__(Mirror)
+        m._lib, m._h, m._keep = self._lib, C.c_void_p(self._lib.spl_gpu_group_member(self._h, i)), None
+        inf = m.info()
+        m._dim, m._slot_count = int(inf.dim), int(inf.slot_count)
+        return m
+
+    def sync(self) -> SyncStats:
+        s = SyncStats()
+        self._check(self._lib.spl_gpu_group_sync(self._h, C.byref(s)))
+        return s
+
+    def fill_synthetic(self, seed_corpus=1234, seed_bloom=99):
+        self._check(self._lib.spl_gpu_group_fill_synthetic(self._h, seed_corpus, seed_bloom))
+
+    def reissued(self) -> int:
+        return int(self._lib.spl_gpu_group_reissued(self._h))
+
+    def search(self, q, k, **kw):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        nq = q.shape[0]
+        p = SearchParams(C.sizeof(SearchParams), nq, q.shape[1], k, kw.get("order", ORDER_COSINE), kw.get("mode", MODE_AUTO),
+                         kw.get("bloom_mask", 0), kw.get("min_similarity", 0.0), kw.get("max_distance", 0.0),
+                         kw.get("exclude_slot", NO_SLOT), 0)
+        out = np.zeros((nq, k), RESULT_DTYPE)
+        counts = np.zeros(nq, np.uint32)
+        self._check(self._lib.spl_gpu_group_search(self._h, C.byref(p), q.ctypes.data, out.ctypes.data, k, counts.ctypes.data))
+        return out, counts

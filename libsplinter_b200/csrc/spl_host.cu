@@ -27,6 +27,7 @@
 #include <atomic>
 #include <chrono>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -253,15 +254,23 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     CUDA_TRY(cudaHostAlloc((void **)&c->h_total, (size_t)kMaxBatchQ * sizeof(uint32_t), cudaHostAllocMapped));
     CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_total, c->h_total, 0));
     memset(c->h_total, 0, (size_t)kMaxBatchQ * sizeof(uint32_t));
-    // staging for sync / dense upload
+    // staging for sync / dense upload.  Sized by the shard: a 4096-slot store must not pay for (and wait on) half a
+    // gigabyte of pinned host memory -- pinning is the slowest part of attaching a small store.
     if (c->sync_threads == 0) {
         unsigned hc = std::thread::hardware_concurrency();
         c->sync_threads = hc ? (hc > 16 ? 16 : hc) : 4;
+        const uint64_t by_size = c->n / 16384 + 1;          // one sweep thread per 16 K slots is plenty
+        if (c->sync_threads > by_size) c->sync_threads = (uint32_t)by_size;
     }
     const size_t row_bytes = (size_t)c->dim * 4;
     c->stage_rows = (uint32_t)((8u << 20) / row_bytes);
+    {
+        const uint64_t share = c->n / c->sync_threads + 1;  // rows one thread stages if every row is dirty
+        if (c->stage_rows > share) c->stage_rows = (uint32_t)share;
+    }
     if (c->stage_rows < 64) c->stage_rows = 64;
     c->stage_meta = 32768;
+    if (c->stage_meta > c->n + 64) c->stage_meta = (uint32_t)c->n + 64;
     c->stage.resize((size_t)c->sync_threads * 4);
     for (size_t i = 0; i < c->stage.size(); i++) {
         StageBuf &b = c->stage[i];
@@ -330,17 +339,27 @@ static int parse_geometry(spl_gpu_ctx *c, const uint8_t *base, size_t size) {
     return 0;
 }
 
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 static spl_gpu_ctx *attach_common(spl_gpu_ctx *c, const spl_gpu_opts *o) {
+    const bool trace = getenv("SPL_GPU_DEBUG_ATTACH") != nullptr;   // developer knob: where does attach time go
+    const double t0 = now_ms();
     c->slot_begin = o ? o->slot_begin : 0;
     uint64_t cnt = o ? o->slot_count : 0;
     if (c->slot_begin >= c->total_slots) { fail(-2, EINVAL, "slot_begin beyond the store"); destroy(c); return nullptr; }
     if (cnt == 0 || c->slot_begin + cnt > c->total_slots) cnt = c->total_slots - c->slot_begin;
     c->n = cnt;
     c->sync_threads = o ? o->sync_threads : 0;
-    if (device_setup(c, o) || alloc_mirror(c, o && (o->flags & SPL_OPT_BF16_MIRROR))) { destroy(c); return nullptr; }
+    if (device_setup(c, o)) { destroy(c); return nullptr; }
+    const double t1 = now_ms();
+    if (alloc_mirror(c, o && (o->flags & SPL_OPT_BF16_MIRROR))) { destroy(c); return nullptr; }
+    const double t2 = now_ms();
     c->c_hash.assign(c->n, 0); c->c_epoch.assign(c->n, 0); c->c_bloom.assign(c->n, 0);
     c->c_flags.assign(c->n, 0); c->c_state.assign(c->n, 0); c->c_fp.assign(c->n, 0); c->c_full.assign(c->n, 0);
     if (spl_gpu_sync(c, nullptr) != 0) { destroy(c); return nullptr; }
+    if (trace)
+        fprintf(stderr, "spl_gpu_attach: device + kernels %.1f ms, mirror + staging allocation %.1f ms, first sync %.1f ms\n",
+                t1 - t0, t2 - t1, now_ms() - t2);
     return c;
 }
 
@@ -1176,15 +1195,34 @@ static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const
     a.out_count = c->d_count;
     a.k = 0;
     c->last_was_tma = false;
-    if (exact) CUDA_TRY(launch_exact_all(a, c->sm_count, c->stream));
-    else CUDA_TRY(launch_scan_fast(a, c->scan_grid, c->stream));
-    CUDA_TRY(launch_sortall(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, cap, c->stream));
-    c->launches += 4;
+    if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+    if (exact) {
+        CUDA_TRY(launch_exact_all(a, c->sm_count, c->stream));
+    } else if (!c->force_ldg && scan_tma_supported(a.dim, 1)) {
+        // the TMA-staged scan in its key-per-row mode: same row traffic as the fused top-k, one 8-byte store per survivor
+        a.k = 1; a.nq = 1;
+        a.cta_cands = c->d_cands_set[c->scan_set]; a.counters = c->d_counters_set[c->scan_set];
+        c->scan_set ^= 1u;
+        CUDA_TRY(launch_scan_tma(a, c->sm_count, c->stream));
+        a.k = 0;
+    } else {
+        CUDA_TRY(launch_scan_fast(a, c->scan_grid, c->stream));
+    }
+    if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+    CUDA_TRY(launch_sortall_select(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, c->d_count, c->stream));
     CUDA_TRY(cudaMemcpyAsync(&c->h_bounce_count, c->d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    if (c->timing) {
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        c->last_scan_ms = ms;   // the scan alone; select + sort + copy-out come on top
+    }
     const uint32_t total = c->h_bounce_count;
     const uint32_t ncopy = total < cap ? total : cap;
-    CUDA_TRY(cudaMemcpy(out, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost));
+    CUDA_TRY(launch_sortall_sort(a, c->d_keys, c->d_sort_tmp, c->sort_tmp_bytes, total, cap, c->stream));
+    c->launches += 5;
+    CUDA_TRY(cudaMemcpyAsync(out, c->d_big_out, (size_t)ncopy * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
     *count = p->k == 0 ? total : ncopy;
     c->h_total[qi] = total;  // the sorted pass counts every survivor
     return 0;
@@ -1399,5 +1437,241 @@ extern "C" int spl_gpu_merge_topk_packed_device(spl_gpu_ctx *c, const void *d_pa
                                   stream ? (cudaStream_t)stream : c->stream, (uint32_t)(block / sizeof(spl_gpu_result)),
                                   (uint32_t)(block / sizeof(uint32_t))));
     c->launches++;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Several GPUs behind one call: one process, one context per GPU over contiguous slot ranges.
+// Every consumer of splinter.h is a C host (splinter.h:21-23); this is what such a host calls instead of
+// orchestrating ranks itself.  Per batch: the per-GPU scans are enqueued on every device's own stream and run side
+// by side; each leaves ONE packed block ([nq][k] records + [nq] counts); the blocks are pulled onto the first device
+// with one peer copy each (3.2 KB per GPU at k = 100 -- inside one process no collective library is needed), merged
+// there with merge_results_kernel, and the merged records come back in one copy.
+// ------------------------------------------------------------------------------------------------
+struct spl_gpu_group {
+    std::vector<spl_gpu_ctx *> ctx;
+    std::vector<cudaEvent_t> done;           // per context: its shard's block is complete (recorded on its stream)
+    std::vector<unsigned char *> d_local;    // per context, on its device: the packed block of the current batch
+    unsigned char *d_blocks = nullptr;       // on device of ctx[0]: all blocks back to back
+    spl_gpu_result *d_fin = nullptr, *h_fin = nullptr;
+    uint32_t *d_fcnt = nullptr, *h_fcnt = nullptr;
+    size_t block_cap = 0;                    // bytes per block the buffers above were sized for
+    uint32_t fin_cap = 0;                    // records
+    std::mutex mu;
+    std::atomic<uint64_t> reissued{0};
+};
+
+static void group_free_buffers(spl_gpu_group *g) {
+    for (size_t i = 0; i < g->ctx.size(); i++) {
+        if (i < g->d_local.size() && g->d_local[i]) { cudaSetDevice(g->ctx[i]->device); cudaFree(g->d_local[i]); g->d_local[i] = nullptr; }
+    }
+    if (!g->ctx.empty()) cudaSetDevice(g->ctx[0]->device);
+    cudaFree(g->d_blocks); cudaFree(g->d_fin); cudaFree(g->d_fcnt); cudaFreeHost(g->h_fin); cudaFreeHost(g->h_fcnt);
+    g->d_blocks = nullptr; g->d_fin = nullptr; g->d_fcnt = nullptr; g->h_fin = nullptr; g->h_fcnt = nullptr;
+    g->block_cap = 0; g->fin_cap = 0;
+}
+
+static int group_ensure_buffers(spl_gpu_group *g, uint32_t nq, uint32_t k) {
+    const size_t bb = SPL_GPU_PACKED_BLOCK_BYTES(nq, k);
+    const uint32_t fin = nq * k;
+    if (bb <= g->block_cap && fin <= g->fin_cap) return 0;
+    for (spl_gpu_ctx *c : g->ctx) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); }
+    group_free_buffers(g);
+    g->d_local.assign(g->ctx.size(), nullptr);
+    for (size_t i = 0; i < g->ctx.size(); i++) {
+        cudaSetDevice(g->ctx[i]->device);
+        if (cudaMalloc((void **)&g->d_local[i], bb) != cudaSuccess) return fail(-1, ENOMEM, "group: cudaMalloc(%zu) failed", bb);
+    }
+    cudaSetDevice(g->ctx[0]->device);
+    if (cudaMalloc((void **)&g->d_blocks, bb * g->ctx.size()) != cudaSuccess || cudaMalloc((void **)&g->d_fin, (size_t)fin * sizeof(spl_gpu_result)) != cudaSuccess ||
+        cudaMalloc((void **)&g->d_fcnt, (size_t)nq * 4) != cudaSuccess)
+        return fail(-1, ENOMEM, "group: cudaMalloc of the merge buffers failed");
+    CUDA_TRY(cudaMallocHost((void **)&g->h_fin, (size_t)fin * sizeof(spl_gpu_result)));
+    CUDA_TRY(cudaMallocHost((void **)&g->h_fcnt, (size_t)nq * 4));
+    g->block_cap = bb; g->fin_cap = fin;
+    return 0;
+}
+
+static spl_gpu_group *group_build(uint32_t n_devices, const int32_t *devices, const spl_gpu_opts *opts, uint64_t total,
+                                  const char *name, uint32_t dense_dim, uint64_t dense_row0) {
+    if (n_devices == 0 || n_devices > 64) { fail(-2, EINVAL, "group needs 1..64 devices"); return nullptr; }
+    spl_gpu_group *g = new spl_gpu_group();
+    const uint64_t per = (total + n_devices - 1) / n_devices;   // contiguous, ceil-divided
+    for (uint32_t i = 0; i < n_devices; i++) {
+        const uint64_t lo = (uint64_t)i * per < total ? (uint64_t)i * per : total;
+        const uint64_t cnt = lo + per <= total ? per : total - lo;
+        if (cnt == 0) break;                                     // more devices than slots: the rest stay idle
+        spl_gpu_opts o;
+        memset(&o, 0, sizeof o);
+        if (opts) o = *opts;
+        o.struct_size = sizeof o;
+        o.device = devices ? devices[i] : (int32_t)i;
+        spl_gpu_ctx *c;
+        if (name) {
+            o.slot_begin = (uint32_t)lo; o.slot_count = (uint32_t)cnt;
+            c = spl_gpu_attach(name, &o);
+        } else {
+            c = spl_gpu_open_dense(cnt, dense_dim, dense_row0 + lo, &o);
+        }
+        if (!c) { for (spl_gpu_ctx *x : g->ctx) destroy(x); delete g; return nullptr; }
+        g->ctx.push_back(c);
+    }
+    g->done.resize(g->ctx.size());
+    for (size_t i = 0; i < g->ctx.size(); i++) {
+        cudaSetDevice(g->ctx[i]->device);
+        if (cudaEventCreateWithFlags(&g->done[i], cudaEventDisableTiming) != cudaSuccess) {
+            fail(-1, EIO, "group: cudaEventCreate failed");
+            for (spl_gpu_ctx *x : g->ctx) destroy(x);
+            delete g;
+            return nullptr;
+        }
+    }
+    return g;
+}
+
+extern "C" spl_gpu_group *spl_gpu_group_attach(const char *name_or_path, uint32_t n_devices, const int32_t *devices,
+                                               const spl_gpu_opts *opts) {
+    if (!name_or_path) { fail(-2, EINVAL, "null store name"); return nullptr; }
+    // the store's slot count decides the shard ranges: read it from the header the way spl_gpu_attach will
+    const bool persistent = opts && (opts->flags & SPL_OPT_PERSISTENT);
+    int fd = persistent ? open(name_or_path, O_RDONLY) : shm_open(name_or_path, O_RDONLY, 0);
+    if (fd < 0) { fail(-1, errno, "cannot open store '%s': %s", name_or_path, strerror(errno)); return nullptr; }
+    uint8_t hdr[16];
+    const ssize_t got = pread(fd, hdr, sizeof hdr, 0);
+    close(fd);
+    uint32_t magic = 0, version = 0, slots = 0;
+    if (got == (ssize_t)sizeof hdr) { memcpy(&magic, hdr, 4); memcpy(&version, hdr + 4, 4); memcpy(&slots, hdr + 8, 4); }
+    if (magic != layout::kMagic || version != layout::kVersion || slots == 0) {
+        fail(-1, EINVAL, "'%s' is not a splinter v%u store", name_or_path, layout::kVersion);
+        return nullptr;
+    }
+    return group_build(n_devices, devices, opts, slots, name_or_path, 0, 0);
+}
+
+extern "C" spl_gpu_group *spl_gpu_group_open_dense(uint64_t n_rows, uint32_t dim, uint32_t n_devices, const int32_t *devices,
+                                                   const spl_gpu_opts *opts) {
+    if (n_rows == 0) { fail(-2, EINVAL, "dense group needs rows"); return nullptr; }
+    return group_build(n_devices, devices, opts, n_rows, nullptr, dim, 0);
+}
+
+extern "C" void spl_gpu_group_detach(spl_gpu_group *g) {
+    if (!g) return;
+    for (spl_gpu_ctx *c : g->ctx) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); }
+    group_free_buffers(g);
+    for (size_t i = 0; i < g->done.size(); i++) { cudaSetDevice(g->ctx[i]->device); cudaEventDestroy(g->done[i]); }
+    for (spl_gpu_ctx *c : g->ctx) destroy(c);
+    delete g;
+}
+
+extern "C" uint32_t spl_gpu_group_size(const spl_gpu_group *g) { return g ? (uint32_t)g->ctx.size() : 0; }
+extern "C" spl_gpu_ctx *spl_gpu_group_member(spl_gpu_group *g, uint32_t i) { return g && i < g->ctx.size() ? g->ctx[i] : nullptr; }
+extern "C" uint64_t spl_gpu_group_reissued(const spl_gpu_group *g) { return g ? g->reissued.load() : 0; }
+
+// every shard sweeps its own slot range, all at once (each context has its own sweep threads and staging)
+extern "C" int spl_gpu_group_sync(spl_gpu_group *g, spl_gpu_sync_stats *total) {
+    if (!g) return fail(-2, EINVAL, "null group");
+    std::vector<spl_gpu_sync_stats> st(g->ctx.size());
+    std::vector<int> rc(g->ctx.size(), 0);
+    std::vector<std::string> err(g->ctx.size());
+    std::vector<std::thread> th;
+    for (size_t i = 0; i < g->ctx.size(); i++)
+        th.emplace_back([&, i] { rc[i] = spl_gpu_sync(g->ctx[i], &st[i]); if (rc[i]) err[i] = g_err; });
+    for (auto &t : th) t.join();
+    for (size_t i = 0; i < g->ctx.size(); i++)
+        if (rc[i]) return fail(rc[i], EIO, "group sync, shard %zu: %s", i, err[i].c_str());
+    if (total) {
+        memset(total, 0, sizeof *total);
+        for (const spl_gpu_sync_stats &x : st) {
+            total->slots_swept += x.slots_swept; total->rows_uploaded += x.rows_uploaded; total->meta_updated += x.meta_updated;
+            total->skipped_busy += x.skipped_busy; total->aba_rechecked += x.aba_rechecked; total->bytes_h2d += x.bytes_h2d;
+            total->rows_revalidated += x.rows_revalidated; total->stale_rows_found += x.stale_rows_found;
+            if (x.sweep_ms > total->sweep_ms) total->sweep_ms = x.sweep_ms;
+            if (x.upload_ms > total->upload_ms) total->upload_ms = x.upload_ms;
+            if (x.generation > total->generation) total->generation = x.generation;
+            total->header_epoch = x.header_epoch;
+        }
+    }
+    return 0;
+}
+
+extern "C" int spl_gpu_group_fill_synthetic(spl_gpu_group *g, uint64_t seed_corpus, uint64_t seed_bloom) {
+    if (!g) return fail(-2, EINVAL, "null group");
+    for (spl_gpu_ctx *c : g->ctx) { int rc = spl_gpu_dense_fill_synthetic(c, seed_corpus, seed_bloom); if (rc) return rc; }
+    return 0;
+}
+
+// one pass over all shards for nq <= q_cap queries already in host memory; merged records land in g->h_fin / h_fcnt
+static int group_pass(spl_gpu_group *g, const spl_gpu_search_params *p, const float *q, uint32_t nq) {
+    const size_t bb = SPL_GPU_PACKED_BLOCK_BYTES(nq, p->k);
+    const size_t coff = SPL_GPU_PACKED_COUNTS_OFFSET(nq, p->k);
+    spl_gpu_search_params pp = *p;
+    pp.nq = nq;
+    int rc;
+    for (size_t i = 0; i < g->ctx.size(); i++) {
+        spl_gpu_ctx *c = g->ctx[i];
+        cudaSetDevice(c->device);
+        std::lock_guard<std::mutex> lk(c->mu);
+        const size_t qbytes = (size_t)nq * c->dim * sizeof(float);
+        memcpy(c->h_q, q, qbytes);
+        CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, qbytes, cudaMemcpyHostToDevice, c->stream));
+        if ((rc = order_before_search(c, c->stream))) return rc;
+        unsigned char *blk = i == 0 ? g->d_blocks : g->d_local[i];   // the first shard writes straight into the merge area
+        rc = search_device_locked(c, &pp, c->d_q, reinterpret_cast<spl_gpu_result *>(blk), p->k,
+                                  reinterpret_cast<uint32_t *>(blk + coff), c->stream);
+        if (rc) { c->counters_dirty = true; order_after_search(c, c->stream); return rc; }
+        if ((rc = order_after_search(c, c->stream))) return rc;
+        CUDA_TRY(cudaEventRecord(g->done[i], c->stream));
+    }
+    spl_gpu_ctx *c0 = g->ctx[0];
+    cudaSetDevice(c0->device);
+    std::lock_guard<std::mutex> lk(c0->mu);
+    for (size_t i = 1; i < g->ctx.size(); i++) {
+        CUDA_TRY(cudaStreamWaitEvent(c0->stream, g->done[i], 0));
+        CUDA_TRY(cudaMemcpyPeerAsync(g->d_blocks + i * bb, c0->device, g->d_local[i], g->ctx[i]->device, bb, c0->stream));
+    }
+    c0->last_was_tma = false;
+    CUDA_TRY(launch_merge_results(reinterpret_cast<const spl_gpu_result *>(g->d_blocks),
+                                  reinterpret_cast<const uint32_t *>(g->d_blocks + coff), (uint32_t)g->ctx.size(), nq, p->k, p->order,
+                                  p->k, g->d_fin, p->k, g->d_fcnt, c0->stream, (uint32_t)(bb / sizeof(spl_gpu_result)),
+                                  (uint32_t)(bb / sizeof(uint32_t))));
+    c0->launches++;
+    CUDA_TRY(cudaMemcpyAsync(g->h_fin, g->d_fin, (size_t)nq * p->k * sizeof(spl_gpu_result), cudaMemcpyDeviceToHost, c0->stream));
+    CUDA_TRY(cudaMemcpyAsync(g->h_fcnt, g->d_fcnt, (size_t)nq * 4, cudaMemcpyDeviceToHost, c0->stream));
+    CUDA_TRY(cudaStreamSynchronize(c0->stream));
+    c0->search_recorded = false;   // (everything this pass enqueued on c0's stream has completed)
+    return 0;
+}
+
+extern "C" int spl_gpu_group_search(spl_gpu_group *g, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
+                                    uint32_t out_stride, uint32_t *counts) {
+    if (!g || g->ctx.empty()) return fail(-2, EINVAL, "null group");
+    int rc = check_params(g->ctx[0], p);
+    if (rc) return rc;
+    if (!q || !out || !counts) return fail(-2, EINVAL, "null buffer");
+    if (p->k == 0 || p->k > SPL_GPU_KMAX_FUSED) return fail(-2, EINVAL, "group search needs k in 1..%u", SPL_GPU_KMAX_FUSED);
+    if (out_stride < p->k) return fail(-2, EINVAL, "out_stride < k");
+    std::lock_guard<std::mutex> lk(g->mu);
+    const uint32_t chunk = g->ctx[0]->q_cap;
+    const uint32_t dim = g->ctx[0]->dim;
+    if ((rc = group_ensure_buffers(g, p->nq < chunk ? p->nq : chunk, p->k))) return rc;
+    for (uint32_t q0 = 0; q0 < p->nq; q0 += chunk) {
+        const uint32_t nq = p->nq - q0 < chunk ? p->nq - q0 : chunk;
+        if ((rc = group_pass(g, p, q + (size_t)q0 * dim, nq))) return rc;
+        for (uint32_t i = 0; i < nq; i++) {
+            counts[q0 + i] = g->h_fcnt[i];
+            if (g->h_fcnt[i] != SPL_GPU_COUNT_UNANSWERED)
+                memcpy(out + (size_t)(q0 + i) * out_stride, g->h_fin + (size_t)i * p->k, (size_t)g->h_fcnt[i] * sizeof(spl_gpu_result));
+        }
+        // what a shard could not answer in the requested mode goes to the fp32 scan, on every shard
+        for (uint32_t i = 0; i < nq; i++) {
+            if (counts[q0 + i] != SPL_GPU_COUNT_UNANSWERED) continue;
+            spl_gpu_search_params one = *p;
+            one.mode = SPL_MODE_FAST;
+            if ((rc = group_pass(g, &one, q + (size_t)(q0 + i) * dim, 1))) return rc;
+            counts[q0 + i] = g->h_fcnt[0];
+            memcpy(out + (size_t)(q0 + i) * out_stride, g->h_fin, (size_t)g->h_fcnt[0] * sizeof(spl_gpu_result));
+            g->reissued++;
+        }
+    }
     return 0;
 }

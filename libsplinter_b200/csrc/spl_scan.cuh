@@ -73,10 +73,12 @@ cudaError_t launch_merge_results(const spl_gpu_result *lists, const uint32_t *co
                                  uint32_t stride, uint32_t order, uint32_t k, spl_gpu_result *out, uint32_t out_stride,
                                  uint32_t *out_count, cudaStream_t stream, uint32_t shard_pitch = 0, uint32_t count_pitch = 0);
 
-// unlimited / k > SPL_GPU_KMAX_FUSED: sort (key, row) pairs of a whole shard and emit records.
-// keys[n] holds the scan's output; tmp buffers are caller-allocated (see sortall_tmp_bytes).
+// unlimited / k > SPL_GPU_KMAX_FUSED: compact the rows holding a key, then sort only those (key, row) pairs and emit
+// records.  keys[n] holds the scan's output; the workspace is caller-allocated (see sortall_tmp_bytes).
 size_t sortall_tmp_bytes(uint32_t n);
-cudaError_t launch_sortall(const ScanArgs &a, uint64_t *keys, void *tmp, size_t tmp_bytes, uint32_t out_cap,
-                           cudaStream_t stream);
+cudaError_t launch_sortall_select(const ScanArgs &a, const uint64_t *keys, void *tmp, size_t tmp_bytes, uint32_t *d_total,
+                                  cudaStream_t stream);
+cudaError_t launch_sortall_sort(const ScanArgs &a, const uint64_t *keys, void *tmp, size_t tmp_bytes, uint32_t total,
+                                uint32_t out_cap, cudaStream_t stream);
 
 }  // namespace spl

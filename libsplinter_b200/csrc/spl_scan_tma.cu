@@ -341,7 +341,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
             }
             nsurv++;
             const uint64_t key = make_key(a.order, sim, dist);
-            if (W.admits(key, row)) W.insert(key, row, lane);
+            if (a.keys_out) {   // unlimited / large-k search: one key per surviving row, sorted afterwards (spl_sortall.cu)
+                if (lane == 0) a.keys_out[row] = key;
+            } else if (W.admits(key, row)) {
+                W.insert(key, row, lane);
+            }
         };
         uint32_t slot = warp, gen = 0;  // this warp's pair index = gen * NP + slot
         if (slot >= NP) { slot -= NP; gen++; }
@@ -494,6 +498,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
             }
             const uint64_t key = make_key(a.order, sim, dist);
             nsurv += __popc(__ballot_sync(0xffffffffu, pass) & group_mask);
+            if (a.keys_out) {   // key-per-row mode (single query with the query in shared memory): see the loop above
+                if (pass) a.keys_out[row] = key;
+                continue;
+            }
             const uint4 st = *my_state;
             const bool admit = pass && ((st.w & 0xffffu) < a.k || better(key, row, ((uint64_t)st.y << 32) | st.x, st.z));
             unsigned m = __ballot_sync(0xffffffffu, admit);
@@ -533,6 +541,17 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
     if (warp == kConsumers && lane == 0) {   // a producer lane: done as soon as the sequence is closed
         asm volatile("griddepcontrol.wait;" ::: "memory");
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    }
+    if (a.keys_out) {   // nothing to merge: the last CTA re-arms the counters for the next launch
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(&a.counters[1], 1u) == gridDim.x - 1) {
+                if (a.total) *a.total = *reinterpret_cast<volatile uint32_t *>(&a.counters[2]);
+                a.counters[0] = 0; a.counters[1] = 0; a.counters[2] = 0;
+            }
+        }
+        return;
     }
     // the row ring is idle now: it becomes the workspace of the final cross-CTA merge
     uint32_t ws_entries = topk_pow2((NP * 2 * RB) / 12 + 1) >> 1;  // largest power of two that fits
