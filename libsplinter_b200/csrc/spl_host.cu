@@ -1456,7 +1456,7 @@ struct spl_gpu_group {
     spl_gpu_result *d_fin = nullptr, *h_fin = nullptr;
     uint32_t *d_fcnt = nullptr, *h_fcnt = nullptr;
     size_t block_cap = 0;                    // bytes per block the buffers above were sized for
-    uint32_t fin_cap = 0;                    // records
+    uint32_t fin_cap = 0, nq_cap = 0;        // records / queries
     std::mutex mu;
     std::atomic<uint64_t> reissued{0};
 };
@@ -1468,13 +1468,16 @@ static void group_free_buffers(spl_gpu_group *g) {
     if (!g->ctx.empty()) cudaSetDevice(g->ctx[0]->device);
     cudaFree(g->d_blocks); cudaFree(g->d_fin); cudaFree(g->d_fcnt); cudaFreeHost(g->h_fin); cudaFreeHost(g->h_fcnt);
     g->d_blocks = nullptr; g->d_fin = nullptr; g->d_fcnt = nullptr; g->h_fin = nullptr; g->h_fcnt = nullptr;
-    g->block_cap = 0; g->fin_cap = 0;
+    g->block_cap = 0; g->fin_cap = 0; g->nq_cap = 0;
 }
 
-static int group_ensure_buffers(spl_gpu_group *g, uint32_t nq, uint32_t k) {
-    const size_t bb = SPL_GPU_PACKED_BLOCK_BYTES(nq, k);
-    const uint32_t fin = nq * k;
-    if (bb <= g->block_cap && fin <= g->fin_cap) return 0;
+static int group_ensure_buffers(spl_gpu_group *g, uint32_t nq_need, uint32_t k) {
+    const size_t bb_need = SPL_GPU_PACKED_BLOCK_BYTES(nq_need, k);
+    const uint32_t fin_need = nq_need * k;
+    if (bb_need <= g->block_cap && fin_need <= g->fin_cap && nq_need <= g->nq_cap) return 0;
+    // grow every capacity to the largest seen so far: calls alternate between shapes (a batch, then single re-issues)
+    const size_t bb = bb_need > g->block_cap ? bb_need : g->block_cap;
+    const uint32_t fin = fin_need > g->fin_cap ? fin_need : g->fin_cap, nq = nq_need > g->nq_cap ? nq_need : g->nq_cap;
     for (spl_gpu_ctx *c : g->ctx) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); }
     group_free_buffers(g);
     g->d_local.assign(g->ctx.size(), nullptr);
@@ -1488,7 +1491,7 @@ static int group_ensure_buffers(spl_gpu_group *g, uint32_t nq, uint32_t k) {
         return fail(-1, ENOMEM, "group: cudaMalloc of the merge buffers failed");
     CUDA_TRY(cudaMallocHost((void **)&g->h_fin, (size_t)fin * sizeof(spl_gpu_result)));
     CUDA_TRY(cudaMallocHost((void **)&g->h_fcnt, (size_t)nq * 4));
-    g->block_cap = bb; g->fin_cap = fin;
+    g->block_cap = bb; g->fin_cap = fin; g->nq_cap = nq;
     return 0;
 }
 
