@@ -294,6 +294,38 @@ int spl_gpu_merge_topk_packed_device(spl_gpu_ctx *ctx, const void *d_packed, uin
                                      uint32_t list_stride, uint32_t order, uint32_t k, spl_gpu_result *d_out,
                                      uint32_t out_stride, uint32_t *d_out_counts, void *stream);
 
+/* ---- the step before the search: bulk embedding of ingested text ---------------------- */
+
+/* The reference's `ingest` command stores a document as VARTEXT chunk slots carrying label 0x200
+ * (splinter_cli_cmd_ingest.c:50-51,140-172) and its splinference daemon embeds them ONE KEY AT A TIME: list the keys,
+ * snapshot each, skip what is not VARTEXT or already has a vector, read the text, run the model, splinter_set_embedding,
+ * check the epoch moved by exactly 2 (splinference.cpp:196-325).  This call is the bulk form of that loop:
+ *   1. spl_gpu_sync, then walk the mirror's host-side metadata for the slots that are enumerate_matches candidates of
+ *      label_mask (0 = every listed key), are typed VARTEXT and whose mirrored vector is still all zero;
+ *   2. copy their texts out of the store's value arena under the seqlock rule (epoch even and unchanged around the copy;
+ *      a busy slot is skipped and left for the next call), `batch` of them at a time;
+ *   3. hand each batch to embed() -- the caller's model; its arithmetic is the caller's business (the reference's is
+ *      llama.cpp + a GGUF file, un-vendored and unpinned: parity at that boundary is unpinned by construction);
+ *   4. write every vector back through set_embedding() -- pass the reference's own splinter_set_embedding: the store
+ *      library stays the only writer of the store -- and, like splinference, count a slot whose epoch did not move by
+ *      exactly 2 as raced (its vector was written, but over newer text; the next call sees it as embedded);
+ *   5. one spl_gpu_sync at the end brings all new vectors into HBM in one pass.
+ * Store-backed contexts only.  Returns 0 / -1 / -2 like every other call; embed() returning non-zero aborts with -1. */
+typedef int (*spl_gpu_embed_fn)(void *user, uint32_t n, const char *const *texts, const uint32_t *text_lens,
+                                uint32_t dim, float *vectors_out /* n x dim */);
+typedef int (*spl_gpu_set_embedding_fn)(const char *key, const float *vec);   /* = splinter_set_embedding (splinter.c:567-588) */
+typedef struct spl_gpu_ingest_stats {
+    uint64_t candidates;     /* slots that matched label / type / zero-vector */
+    uint64_t embedded;       /* vectors written and confirmed (epoch moved by exactly 2) */
+    uint64_t skipped_busy;   /* text could not be read consistently (writer active): left for the next call */
+    uint64_t raced;          /* written, but the slot's epoch moved by more than 2 meanwhile */
+    uint64_t write_failed;   /* set_embedding() refused (slot busy or gone) */
+    uint64_t batches;
+    double   gather_ms, embed_ms, write_ms, sync_ms;
+} spl_gpu_ingest_stats;
+int spl_gpu_ingest_embeddings(spl_gpu_ctx *ctx, uint64_t label_mask, uint32_t batch, spl_gpu_embed_fn embed, void *user,
+                              spl_gpu_set_embedding_fn set_embedding, spl_gpu_ingest_stats *stats /* nullable */);
+
 /* ---- several GPUs behind one call ---------------------------------------------------------------------------- */
 
 /* One process, one context per GPU, each mirroring a contiguous slot range [i*ceil(N/G), ...) of the same store

@@ -24,6 +24,7 @@ ABI_SYMBOLS = [
     "spl_gpu_get_counters", "spl_gpu_find_key", "spl_gpu_merge_topk_packed_device",
     "spl_gpu_group_attach", "spl_gpu_group_open_dense", "spl_gpu_group_detach", "spl_gpu_group_size", "spl_gpu_group_member",
     "spl_gpu_group_sync", "spl_gpu_group_fill_synthetic", "spl_gpu_group_search", "spl_gpu_group_reissued",
+    "spl_gpu_ingest_embeddings",
 ]
 
 ORDER_COSINE, ORDER_L2 = 0, 1
@@ -53,6 +54,12 @@ class SyncStats(C.Structure):
                 ("meta_updated", C.c_uint64), ("skipped_busy", C.c_uint64), ("aba_rechecked", C.c_uint64),
                 ("bytes_h2d", C.c_uint64), ("sweep_ms", C.c_double), ("upload_ms", C.c_double),
                 ("header_epoch", C.c_uint64), ("rows_revalidated", C.c_uint64), ("stale_rows_found", C.c_uint64)]
+
+
+class IngestStats(C.Structure):
+    _fields_ = [("candidates", C.c_uint64), ("embedded", C.c_uint64), ("skipped_busy", C.c_uint64), ("raced", C.c_uint64),
+                ("write_failed", C.c_uint64), ("batches", C.c_uint64), ("gather_ms", C.c_double), ("embed_ms", C.c_double),
+                ("write_ms", C.c_double), ("sync_ms", C.c_double)]
 
 
 class Counters(C.Structure):
@@ -137,6 +144,8 @@ def load() -> C.CDLL:
     lib.spl_gpu_group_search.argtypes = [vp, C.POINTER(SearchParams), vp, vp, u32, vp]
     lib.spl_gpu_group_reissued.restype = u64
     lib.spl_gpu_group_reissued.argtypes = [vp]
+    lib.spl_gpu_ingest_embeddings.restype = C.c_int
+    lib.spl_gpu_ingest_embeddings.argtypes = [vp, u64, u32, vp, vp, vp, C.POINTER(IngestStats)]
     lib.spl_gpu_scan_noalloc.restype = C.c_int
     lib.spl_gpu_scan_noalloc.argtypes = [vp, vp, vp, vp, u64, u64, C.POINTER(SearchParams), vp, vp, u32, vp, vp]
     lib.spl_gpu_slot_meta.restype = C.c_int
@@ -312,6 +321,14 @@ class Mirror:
         self._check(self._lib.spl_gpu_merge_topk_packed_device(self._h, C.c_void_p(d_packed), nlists, nq, stride, order, k,
                                                                C.c_void_p(d_out), out_stride, C.c_void_p(d_out_counts),
                                                                C.c_void_p(stream)))
+
+    def ingest_embeddings(self, label_mask, batch, embed_fn_ptr, user_ptr, set_embedding_fn_ptr) -> IngestStats:
+        """embed_fn_ptr / set_embedding_fn_ptr: C function pointers (ctypes functions or addresses)"""
+        st = IngestStats()
+        as_vp = lambda f: C.cast(f, C.c_void_p)  # noqa: E731
+        self._check(self._lib.spl_gpu_ingest_embeddings(self._h, label_mask, batch, as_vp(embed_fn_ptr), C.c_void_p(user_ptr),
+                                                        as_vp(set_embedding_fn_ptr), C.byref(st)))
+        return st
 
     def find_key(self, key: str):
         """slot index of `key` in the live store, or None"""

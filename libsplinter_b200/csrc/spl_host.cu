@@ -24,6 +24,7 @@
 #include <time.h>
 #include <unistd.h>
 
+#include <array>
 #include <atomic>
 #include <chrono>
 #include <mutex>
@@ -1677,4 +1678,83 @@ extern "C" int spl_gpu_group_search(spl_gpu_group *g, const spl_gpu_search_param
         }
     }
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// bulk embedding of ingested text; contract in include/splinter_gpu.h
+// ------------------------------------------------------------------------------------------------
+extern "C" int spl_gpu_ingest_embeddings(spl_gpu_ctx *c, uint64_t label_mask, uint32_t batch, spl_gpu_embed_fn embed, void *user,
+                                         spl_gpu_set_embedding_fn set_embedding, spl_gpu_ingest_stats *stats) {
+    using namespace layout;
+    if (!c || !embed || !set_embedding) return fail(-2, EINVAL, "null argument");
+    if (c->dense || !c->base) return fail(-2, EINVAL, "dense contexts have no store to ingest from");
+    if (batch == 0) batch = 256;
+    constexpr size_t S_VAL_OFF = 16, S_TYPE = 24;
+    constexpr uint8_t kVartext = 1u << 7;                       // SPL_SLOT_TYPE_VARTEXT, splinter.h:89
+    uint32_t maxval;
+    memcpy(&maxval, c->base + H_MAXVAL, 4);
+    const uint8_t *values = c->base + kHeaderSize + (size_t)c->total_slots * c->slot_size;   // splinter.c:107-109
+    spl_gpu_ingest_stats st;
+    memset(&st, 0, sizeof st);
+    int rc = spl_gpu_sync(c, nullptr);
+    if (rc) return rc;
+    // candidates, in slot order (the order splinter_list hands keys to the daemon's backfill, splinter.c:466-477)
+    std::vector<uint32_t> cand;
+    std::unique_lock<std::mutex> caches(c->sweep_mu);           // the host caches belong to the sweep
+    for (uint64_t r = 0; r < c->n; r++) {
+        if (!(c->c_flags[r] & SPL_ROW_ENUM) || (c->c_bloom[r] & label_mask) != label_mask) continue;
+        if (!(c->c_flags[r] & SPL_ROW_LIST)) continue;          // no value, nothing to embed
+        if (c->c_state[r] & 2) continue;                        // the mirrored vector is not zero: embedded already
+        const uint8_t *sl = c->base + kHeaderSize + (c->slot_begin + r) * c->slot_size;
+        if (!(sl[S_TYPE] & kVartext)) continue;
+        cand.push_back((uint32_t)r);
+    }
+    caches.unlock();
+    st.candidates = cand.size();
+    std::vector<char> text((size_t)batch * ((size_t)maxval + 1));
+    std::vector<const char *> ptrs(batch);
+    std::vector<uint32_t> lens(batch), rows(batch);
+    std::vector<uint64_t> epochs(batch);
+    std::vector<std::array<char, 64>> keys(batch);
+    std::vector<float> vecs((size_t)batch * c->dim);
+    for (size_t i0 = 0; i0 < cand.size();) {
+        auto t0 = std::chrono::steady_clock::now();
+        uint32_t nb = 0;
+        for (; i0 < cand.size() && nb < batch; i0++) {
+            const uint32_t r = cand[i0];
+            const uint8_t *sl = c->base + kHeaderSize + (c->slot_begin + r) * c->slot_size;
+            const uint64_t e1 = ld_acq64(sl + S_EPOCH);
+            if (e1 & 1) { st.skipped_busy++; continue; }        // writer active (splinference.cpp:201)
+            const uint32_t off = ld_acq32(sl + S_VAL_OFF), len = ld_acq32(sl + S_VAL_LEN);
+            if (len == 0 || len > maxval || (uint64_t)off + len > (uint64_t)c->total_slots * maxval) { st.skipped_busy++; continue; }
+            char *dst = text.data() + (size_t)nb * ((size_t)maxval + 1);
+            memcpy(dst, values + off, len);
+            dst[len] = '\0';
+            memcpy(keys[nb].data(), sl + S_KEY, 64);
+            keys[nb][63] = '\0';
+            std::atomic_thread_fence(std::memory_order_acquire);
+            if (ld_acq64(sl + S_EPOCH) != e1 || ld_acq64(sl + S_HASH) == 0) { st.skipped_busy++; continue; }
+            ptrs[nb] = dst; lens[nb] = len; rows[nb] = r; epochs[nb] = e1;
+            nb++;
+        }
+        auto t1 = std::chrono::steady_clock::now();
+        st.gather_ms += std::chrono::duration<double, std::milli>(t1 - t0).count();
+        if (nb == 0) continue;
+        if (embed(user, nb, ptrs.data(), lens.data(), c->dim, vecs.data()) != 0)
+            return fail(-1, EIO, "the embed callback failed on a batch of %u texts", nb);
+        auto t2 = std::chrono::steady_clock::now();
+        st.embed_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
+        for (uint32_t i = 0; i < nb; i++) {
+            if (set_embedding(keys[i].data(), vecs.data() + (size_t)i * c->dim) != 0) { st.write_failed++; continue; }
+            const uint8_t *sl = c->base + kHeaderSize + (c->slot_begin + rows[i]) * c->slot_size;
+            if (ld_acq64(sl + S_EPOCH) == epochs[i] + 2) st.embedded++; else st.raced++;   // splinference.cpp:282-286
+        }
+        st.write_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t2).count();
+        st.batches++;
+    }
+    auto t3 = std::chrono::steady_clock::now();
+    rc = spl_gpu_sync(c, nullptr);
+    st.sync_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t3).count();
+    if (stats) *stats = st;
+    return rc;
 }
