@@ -422,11 +422,25 @@ def run_ours(args):
     if rank == 0:
         gbs = job_bytes / ms_step / 1e6
         per_gpu_bytes = job_bytes / world
-        traffic = None
+        traffic, traffic_note = None, None
         tp = ROOT / "profiles" / "roofline_traffic.json"
         if tp.exists():
             tj = json.loads(tp.read_text())
-            traffic = tj.get("c2_mask3_dram_bytes_per_launch") if single else tj.get("c4_dram_bytes_per_launch_by_gpus", {}).get(str(world))
+            if single:
+                # DRAM bytes per launch from the committed ncu capture -- but only if that capture was taken from the
+                # kernel sources this run was built from
+                sys.path.insert(0, str(ROOT / "tools"))
+                from roofline_traffic import kernel_sha16
+                cap = tj.get("c2_mask3_capture", {})
+                if cap.get("kernel_source_sha16") == kernel_sha16():
+                    traffic = tj.get("c2_mask3_dram_bytes_per_launch")
+                    traffic_note = f"ncu --set full, {cap.get('report')}, kernel sources {cap.get('kernel_source_sha16')}"
+                else:
+                    traffic_note = ("the committed capture belongs to other kernel sources (" + str(cap.get("kernel_source_sha16")) +
+                                    " vs " + kernel_sha16() + "): not reported")
+            else:
+                traffic = tj.get("c4_dram_bytes_per_launch_by_gpus", {}).get(str(world))
+                traffic_note = tj.get("_source_c4", "")[:120]
         line = {
             "metric": "scanned_GB_per_s", "value": round(gbs, 2), "unit": "GB/s",
             "queries_per_s": round(1e3 / ms_step, 2),
@@ -438,7 +452,7 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(per_gpu_bytes / ms_step / 1e6, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(per_gpu_bytes / ms_step / 1e6 / peak, 4), "traffic": traffic,
+                         "frac": round(per_gpu_bytes / ms_step / 1e6 / peak, 4), "traffic": traffic, "traffic_source": traffic_note,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": int(per_gpu_bytes),
                          "kernel": "spl::scan_*_kernel (one launch per query per GPU)"},
             "parity": parity,
@@ -514,12 +528,20 @@ def c3_batched_leg(sg, support, torch, dev, stream, args):
         except AssertionError:
             ok = False
         flops = 2.0 * nq * n * dim
-        return {"workload": "C3: 2^20 slots x 1024-d, 256 queries, L2 top-32, bf16 tcgen05 contraction + fp32 re-rank",
+        cnts = m.counters()
+        tf_sustained = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        return {"workload": "C3: 2^20 slots x 1024-d, 256 queries, L2 top-32, bf16 tcgen05 contraction + fp32 re-rank + selection proof",
+                "selection_proof": {"queries_through_host_call": int(cnts.batch_queries), "answered_by_fp32_fallback": int(cnts.batch_unproven),
+                                    "rows_rescored_beyond_2k": int(cnts.batch_rescored_extra),
+                                    "device_call_unanswered": int((cnt == -1).sum().item())},
+                "frac_of_sustained_peak": round(flops / ms / 1e9 / tf_sustained, 4),
                 "ms_per_batch": round(ms, 4), "queries_per_s": round(nq / ms * 1e3, 1),
                 "e2e_ms_per_batch": round(ms_e2e, 4), "e2e_queries_per_s": round(nq / ms_e2e * 1e3, 1),
                 "roofline": {"bound": "tensor", "achieved": round(flops / ms / 1e9, 1), "peak": tf_peak, "unit": "TFLOP/s",
                              "frac": round(flops / ms / 1e9 / tf_peak, 4),
-                             "note": "algorithmic flops 2*nq*n*D per batch; the 1/16 sampling pass is extra work not counted"},
+                             "note": "algorithmic flops 2*nq*n*D per batch (the 1/64 sampling pass is extra work, not counted); peak = the "
+                                     "measured cuBLAS bf16 BURST; the batch loop runs power-capped at ~1.4 GHz, where cuBLAS itself "
+                                     "sustains bf16_tflops_sustained -- frac_of_sustained_peak is against that"},
                 "hbm_GB_per_s": round((2.0 * n * dim + 13.0 * n) / ms / 1e6, 1),
                 "parity": {"ok": ok, "indices_identical": ident, "checked_queries": 8, "checked_slots": sample},
                 "all_counts_full": bool(int(cnt.min()) == k)}

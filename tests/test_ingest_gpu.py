@@ -73,7 +73,7 @@ def test_bulk_ingest_writes_what_the_per_key_loop_writes():
             assert st.skipped_busy == 0 and st.raced == 0 and st.write_failed == 0 and seen.value == NCHUNK
             assert st.batches == -(-NCHUNK // 512)
             sec_b = (st.gather_ms + st.embed_ms + st.write_ms) / 1e3
-            print(f"\\nembedding {NCHUNK} chunks: per-key loop {NCHUNK / float(sec_a):,.0f} keys/s, bulk {NCHUNK / sec_b:,.0f} keys/s "
+            print(f"embedding {NCHUNK} chunks: per-key loop {NCHUNK / float(sec_a):,.0f} keys/s, bulk {NCHUNK / sec_b:,.0f} keys/s "
                   f"(gather {st.gather_ms:.1f} ms, stub model {st.embed_ms:.1f} ms, write-back {st.write_ms:.1f} ms, "
                   f"one sync of {NCHUNK} rows {st.sync_ms:.1f} ms)")
             ref.splinter_close()
