@@ -222,6 +222,11 @@ def run_ours(args):
             raise SystemExit("launch multi-GPU runs with torch.distributed.run (one rank per GPU)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # the contract is ONE JSON line on stdout: whatever libraries print while they initialise (NCCL announces its
+    # version there) goes to stderr; stdout comes back just before the line is printed
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -476,7 +481,9 @@ def run_ours(args):
             line["c5_mixed"] = c5
         if single and not args.skip_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(k, head_mask)
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(line), flush=True)
     m.close()
     if world > 1:
         dist.barrier()

@@ -1365,11 +1365,26 @@ static int search_host_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             const uint32_t nq = (p->nq - q0 < c->q_cap) ? p->nq - q0 : c->q_cap;
             spl_gpu_search_params pp = *p;
             pp.nq = nq;
-            memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
-            CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
-            if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
             memset(c->h_total + q0, 0, nq * sizeof(uint32_t));  // mapped memory; ordered before the launch below
-            if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream, c->m_total + q0))) return rc;
+            uint32_t fmode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
+            if (nq == 1 && fmode == SPL_MODE_FAST && !c->force_ldg && scan_tma_qparam_supported(c->dim, p->k)) {
+                // one query: it rides inside the launch (kernel parameter space) -- no host-to-device copy of its own
+                ScanArgs a;
+                fill_args(c, &pp, a);
+                a.q = nullptr;
+                a.out = c->m_out; a.out_count = c->m_count; a.total = c->m_total + q0;
+                a.out_stride = p->k; a.count_stride = 1;
+                c->scan_set ^= 1u;
+                if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+                CUDA_TRY(launch_scan_tma_qparam(a, q + (size_t)q0 * c->dim, c->sm_count, c->stream));
+                c->last_was_tma = true; c->last_tma_stream = c->stream;
+                c->launches++;
+            } else {
+                memcpy(c->h_q, q + (size_t)q0 * c->dim, nq * qbytes);
+                CUDA_TRY(cudaMemcpyAsync(c->d_q, c->h_q, nq * qbytes, cudaMemcpyHostToDevice, c->stream));
+                if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+                if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream, c->m_total + q0))) return rc;
+            }
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
             CUDA_TRY(cudaStreamSynchronize(c->stream));
             if (c->timing) {

@@ -65,6 +65,9 @@ bool scan_tma_supported(uint32_t dim, uint32_t k);
 bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq);
 cudaError_t scan_tma_prepare();
 cudaError_t launch_scan_tma(const ScanArgs &a, int grid, cudaStream_t stream);
+// one query handed over inside the launch (kernel parameter space) instead of through a device buffer
+bool scan_tma_qparam_supported(uint32_t dim, uint32_t k);
+cudaError_t launch_scan_tma_qparam(const ScanArgs &a, const float *q_host, int grid, cudaStream_t stream);
 
 cudaError_t merge_prepare();
 // merge nlists lists of Cand-like results (spl_gpu_result records) into the top-k; shard_pitch (records) / count_pitch

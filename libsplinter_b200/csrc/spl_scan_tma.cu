@@ -19,6 +19,7 @@
 // One persistent CTA per SM keeps up to ~190 KB of row data in flight per SM no matter what the
 // compute warps are doing -- what an HBM-bound gather of 3 KB rows needs.
 #include <float.h>
+#include <string.h>
 
 #include <type_traits>
 
@@ -143,8 +144,28 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32
     return L;
 }
 
+// The host-buffer call's single query can travel INSIDE the launch (kernel parameter space, 4*dim bytes) instead of
+// through a host-to-device copy of its own: one operation less on the stream between the caller and its answer.
+template <int V>
+struct QueryArg { float4 v[V * 32]; };
+struct NoQueryArg { float4 v[1]; };
+
+template <int V, int NQ, bool QP>
+__device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *qparam);
+
 template <int V, int NQ>
 __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs a) {
+    scan_tma_body<V, NQ, false>(a, nullptr);
+}
+
+// (only instantiated for NQ = 1 and dimensions whose query fits the classic 4 KB parameter space next to ScanArgs)
+template <int V>
+__global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_qparam_kernel(const ScanArgs a, const __grid_constant__ QueryArg<V> q) {
+    scan_tma_body<V, 1, true>(a, q.v);
+}
+
+template <int V, int NQ, bool QP>
+__device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *qparam) {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint32_t s_flag;
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
@@ -316,7 +337,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) scan_tma_kernel(const ScanArgs
         }
     } else if constexpr (!QS) {
         // ================================ consumers ================================
-        const float4 *q4 = reinterpret_cast<const float4 *>(a.q);
+        const float4 *q4 = QP ? qparam : reinterpret_cast<const float4 *>(a.q);
         float4 qv[V];
         float ma = 0.f;
 #pragma unroll
@@ -628,7 +649,41 @@ cudaError_t scan_tma_prepare() {
     if ((e = prepare_v<8>(bytes))) return e;
     if ((e = prepare_v<4>(bytes))) return e;
     if ((e = prepare_v<2>(bytes))) return e;
-    return prepare_v<1>(bytes);
+    if ((e = prepare_v<1>(bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_qparam_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_qparam_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(scan_tma_qparam_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    return cudaFuncSetAttribute(scan_tma_qparam_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+template <int V>
+static cudaError_t launch_qparam_v(const ScanArgs &a, const float *q_host, int grid, cudaStream_t stream) {
+    const TmaLayout L = tma_layout(a.dim, a.k, 1);
+    QueryArg<V> q;
+    memcpy(q.v, q_host, sizeof q.v);
+    scan_tma_qparam_kernel<V><<<grid, kTmaThreads, L.total, stream>>>(a, q);
+    return cudaGetLastError();
+}
+
+bool scan_tma_qparam_supported(uint32_t dim, uint32_t k) {
+    return (dim == 768 || dim == 512 || dim == 256 || dim == 128) && scan_tma_supported(dim, k) && !tma_query_in_smem(dim, 1);
+}
+
+// single query handed over in the launch's parameter space (host pointer q_host, 4*dim bytes, read before returning)
+cudaError_t launch_scan_tma_qparam(const ScanArgs &a_in, const float *q_host, int grid, cudaStream_t stream) {
+    ScanArgs a = a_in;
+    const uint32_t ngroups = (a.n + 31u) >> 5;
+    uint32_t cg = 8;
+    while (cg > 1 && ngroups / cg < (uint32_t)grid * kProducers * 4u) cg >>= 1;
+    a.chunk_groups = cg;
+    a.nq = 1;
+    switch (a.dim) {
+        case 768: return launch_qparam_v<6>(a, q_host, grid, stream);
+        case 512: return launch_qparam_v<4>(a, q_host, grid, stream);
+        case 256: return launch_qparam_v<2>(a, q_host, grid, stream);
+        case 128: return launch_qparam_v<1>(a, q_host, grid, stream);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 cudaError_t launch_scan_tma(const ScanArgs &a_in, int grid, cudaStream_t stream) {
