@@ -298,10 +298,13 @@ def run_ours(args):
     def timed_e2e(mask, steps, warmup):
         """host query in pinned memory -> H2D, scan (+ gather/merge), D2H of the hits, every step"""
         qbuf = torch.empty(DIM, dtype=torch.float32, device=dev)
+        hp = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask)
+        h_out, h_cnt = np.zeros((1, k), sg.RESULT_DTYPE), np.zeros(1, np.uint32)
 
         def one(i):
             if single:
-                m.search(q_host[i % N_QUERIES], k, bloom_mask=mask)  # the host-buffer C-ABI call itself
+                # the host-buffer C-ABI call itself: query in host memory in, records in host memory out
+                m.search_into(hp, q_host[i % N_QUERIES], h_out, k, h_cnt)
             else:
                 qbuf.copy_(q_pin[i % N_QUERIES], non_blocking=True)
                 device_step(i, mask, qsrc=qbuf)

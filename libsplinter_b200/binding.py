@@ -302,6 +302,13 @@ class Mirror:
                                              counts.ctypes.data))
         return out, counts
 
+    def search_into(self, p: SearchParams, q: np.ndarray, out: np.ndarray, out_stride: int, counts: np.ndarray):
+        """spl_gpu_search with caller-owned host buffers and a prepared parameter block: the C call and nothing else
+        (what a C host pays per query; `search` above adds array set-up on every call)."""
+        rc = self._lib.spl_gpu_search(self._h, C.byref(p), q.ctypes.data, out.ctypes.data, out_stride, counts.ctypes.data)
+        if rc != 0:
+            self._check(rc)
+
     def search_device(self, p: SearchParams, d_q: int, d_out: int, out_stride: int, d_counts: int, stream: int = 0):
         self._check(self._lib.spl_gpu_search_device(self._h, C.byref(p), C.c_void_p(d_q), C.c_void_p(d_out),
                                                     out_stride, C.c_void_p(d_counts), C.c_void_p(stream)))

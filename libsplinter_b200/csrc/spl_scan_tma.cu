@@ -122,7 +122,7 @@ __host__ __device__ constexpr bool tma_query_in_smem(uint32_t dim, uint32_t nq) 
 
 // nq > 1 (small-batch scan): nq * kConsumers lists of k entries, their bookkeeping words and the nq
 // queries themselves live in shared memory as well; the ring gets what is left.
-__host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32_t nq = 1) {
+__host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32_t nq = 1, bool stage_q = false) {
     TmaLayout L;
     L.row_bytes = dim * 4;
     L.list_entries = nq * scan_topk_entries(k, kConsumers);   // per query: kConsumers lists of k entries, padded to a power of two
@@ -132,7 +132,7 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32
     L.meta_off = L.empty_off + kMaxPairs * 8;                     // uint4 {row0, flags0, row1, flags1}
     L.clist_off = L.meta_off + kMaxPairs * 16;                    // per producer warp: 256 x {row, flags}
     L.state_off = L.clist_off + kProducers * 256 * 8;             // nq > 1: uint4 per (query, consumer warp)
-    const bool qs = tma_query_in_smem(dim, nq);
+    const bool qs = tma_query_in_smem(dim, nq) || stage_q;   // stage_q: a query that arrived in the launch's parameter space
     L.q_off = L.state_off + (qs ? nq * kConsumers * 20u + 16u : 0u);  // + u32 survivors per list, |q|^2 per query
                                                                   // then the queries, fp32 [nq][dim]
     L.rows_off = (L.q_off + (qs ? nq * L.row_bytes : 0u) + 127u) & ~127u;
@@ -170,7 +170,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     __shared__ uint32_t s_flag;
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const TmaLayout L = tma_layout(a.dim, a.k, NQ);
+    const TmaLayout L = tma_layout(a.dim, a.k, NQ, QP);
     const uint32_t list_entries = L.list_entries;
     const uint32_t qstride = list_entries / NQ;   // list entries per query
     uint64_t *skeys = reinterpret_cast<uint64_t *>(smem);
@@ -196,6 +196,16 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
         float4 *sq4 = reinterpret_cast<float4 *>(smem + L.q_off);
         const float4 *gq4 = reinterpret_cast<const float4 *>(a.q);
         for (uint32_t i = threadIdx.x; i < NQ * (a.dim >> 2); i += blockDim.x) sq4[i] = gq4[i];
+    }
+    if constexpr (QP) {
+        // Parameter space is read through the constant cache, which serves ONE address per request: a lane-indexed read
+        // (32 addresses per instruction, 16 warps x 6 instructions) cost ~100 us per launch.  Read it warp-uniformly
+        // instead -- every warp takes a slice, one address per instruction -- and park the query in shared memory.
+        float4 *sq4 = reinterpret_cast<float4 *>(smem + L.q_off);
+        for (uint32_t i = warp; i < (uint32_t)V * 32u; i += kConsumers + kProducers) {
+            const float4 v = qparam[i];
+            if (lane == 0) sq4[i] = v;
+        }
     }
     __syncthreads();
 
@@ -337,7 +347,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
         }
     } else if constexpr (!QS) {
         // ================================ consumers ================================
-        const float4 *q4 = QP ? qparam : reinterpret_cast<const float4 *>(a.q);
+        const float4 *q4 = QP ? reinterpret_cast<const float4 *>(smem + L.q_off) : reinterpret_cast<const float4 *>(a.q);
         float4 qv[V];
         float ma = 0.f;
 #pragma unroll
@@ -658,7 +668,7 @@ cudaError_t scan_tma_prepare() {
 
 template <int V>
 static cudaError_t launch_qparam_v(const ScanArgs &a, const float *q_host, int grid, cudaStream_t stream) {
-    const TmaLayout L = tma_layout(a.dim, a.k, 1);
+    const TmaLayout L = tma_layout(a.dim, a.k, 1, true);
     QueryArg<V> q;
     memcpy(q.v, q_host, sizeof q.v);
     scan_tma_qparam_kernel<V><<<grid, kTmaThreads, L.total, stream>>>(a, q);
@@ -666,7 +676,8 @@ static cudaError_t launch_qparam_v(const ScanArgs &a, const float *q_host, int g
 }
 
 bool scan_tma_qparam_supported(uint32_t dim, uint32_t k) {
-    return (dim == 768 || dim == 512 || dim == 256 || dim == 128) && scan_tma_supported(dim, k) && !tma_query_in_smem(dim, 1);
+    return (dim == 768 || dim == 512 || dim == 256 || dim == 128) && !tma_query_in_smem(dim, 1) &&
+           tma_layout(dim, k, 1, true).pairs >= kMinPairs;
 }
 
 // single query handed over in the launch's parameter space (host pointer q_host, 4*dim bytes, read before returning)
