@@ -373,7 +373,7 @@ def run_ours(args):
         out4 = torch.zeros((4 * k, 32), dtype=torch.uint8, device=dev)
         cnt4 = torch.zeros(4, dtype=torch.int32, device=dev)
         for name, mask in (("mask_0x3", C2_MASK), ("mask_all_match_bit63", 1 << 63)):
-            p4 = m.params(4, k, mode=sg.MODE_FAST, bloom_mask=mask)
+            p4 = m.params(4, k, mode=sg.MODE_FAST, bloom_mask=mask, flags=sg.SEARCH_PIPELINED)   # a loop of calls on one stream
             for _ in range(args.warmup):
                 m.search_device(p4, q4.data_ptr(), out4.data_ptr(), k, cnt4.data_ptr(), stream)
             barrier()

@@ -124,6 +124,8 @@ struct spl_gpu_ctx {
     spl_gpu_result h_bounce[SPL_GPU_KMAX_FUSED];  // small host bounce buffers for the retry paths
     uint32_t h_bounce_count = 0;
     uint32_t *h_total = nullptr, *m_total = nullptr;  // mapped: rows that survived predicate + thresholds, per query
+    uint32_t *h_seq = nullptr, *m_seq = nullptr;      // mapped: completion word of the host-buffer fused search (see wait_answer)
+    uint32_t seq = 0;
     uint32_t last_nq = 0;
     spl_gpu_result *m_out = nullptr;  // device views of the mapped host buffers h_out / h_count
     uint32_t *m_count = nullptr;
@@ -255,6 +257,9 @@ static int alloc_mirror(spl_gpu_ctx *c, bool bf16) {
     CUDA_TRY(cudaHostAlloc((void **)&c->h_total, (size_t)kMaxBatchQ * sizeof(uint32_t), cudaHostAllocMapped));
     CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_total, c->h_total, 0));
     memset(c->h_total, 0, (size_t)kMaxBatchQ * sizeof(uint32_t));
+    CUDA_TRY(cudaHostAlloc((void **)&c->h_seq, 64, cudaHostAllocMapped));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&c->m_seq, c->h_seq, 0));
+    memset(c->h_seq, 0, 64);
     // staging for sync / dense upload.  Sized by the shard: a 4096-slot store must not pay for (and wait on) half a
     // gigabyte of pinned host memory -- pinning is the slowest part of attaching a small store.
     if (c->sync_threads == 0) {
@@ -301,7 +306,7 @@ static void destroy(spl_gpu_ctx *c) {
     cudaFree(c->d_batch); cudaFree(c->d_qbatch); cudaFree(c->d_bout); cudaFree(c->d_bcount);
     cudaFreeHost(c->h_bout); cudaFreeHost(c->h_bcount);
     cudaFree(c->d_keys); cudaFree(c->d_sort_tmp); cudaFree(c->d_big_out); cudaFree(c->d_synth_scale);
-    cudaFreeHost(c->h_q); cudaFreeHost(c->h_out); cudaFreeHost(c->h_count); cudaFreeHost(c->h_total);
+    cudaFreeHost(c->h_q); cudaFreeHost(c->h_out); cudaFreeHost(c->h_count); cudaFreeHost(c->h_total); cudaFreeHost(c->h_seq);
     for (StageBuf &b : c->stage) {
         cudaFreeHost(b.h_rows); cudaFreeHost(b.h_meta); cudaFree(b.d_rows); cudaFree(b.d_meta);
         if (b.ev) cudaEventDestroy(b.ev);
@@ -1232,6 +1237,21 @@ static int search_one_full(spl_gpu_ctx *c, const spl_gpu_search_params *p, const
 static int search_host_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
                               uint32_t out_stride, uint32_t *counts);
 
+// The fused scan writes its records straight into mapped host memory; its last CTA then sets a completion word.  Polling
+// that word returns the answer a few microseconds before cudaStreamSynchronize would (which waits for the driver to
+// notice the kernel's retirement).  A launch that faults never sets the word: after a bounded spin the stream is
+// synchronised the ordinary way, which also surfaces the error.
+static int wait_answer(spl_gpu_ctx *c, uint32_t expect) {
+    const auto t0 = std::chrono::steady_clock::now();
+    for (uint32_t spins = 0;; spins++) {
+        if (__atomic_load_n(c->h_seq, __ATOMIC_ACQUIRE) == expect) return 0;
+        if ((spins & 1023u) == 1023u && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20)) break;
+        __builtin_ia32_pause();
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
 extern "C" int spl_gpu_search(spl_gpu_ctx *c, const spl_gpu_search_params *p, const float *q, spl_gpu_result *out,
                               uint32_t out_stride, uint32_t *counts) {
     int rc = check_params(c, p);
@@ -1367,13 +1387,15 @@ static int search_host_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
             pp.nq = nq;
             memset(c->h_total + q0, 0, nq * sizeof(uint32_t));  // mapped memory; ordered before the launch below
             uint32_t fmode = p->mode == SPL_MODE_AUTO ? SPL_MODE_FAST : p->mode;
-            if (nq == 1 && fmode == SPL_MODE_FAST && !c->force_ldg && scan_tma_qparam_supported(c->dim, p->k)) {
+            const bool polled = nq == 1 && fmode == SPL_MODE_FAST && !c->force_ldg && scan_tma_qparam_supported(c->dim, p->k);
+            if (polled) {
                 // one query: it rides inside the launch (kernel parameter space) -- no host-to-device copy of its own
                 ScanArgs a;
                 fill_args(c, &pp, a);
                 a.q = nullptr;
                 a.out = c->m_out; a.out_count = c->m_count; a.total = c->m_total + q0;
                 a.out_stride = p->k; a.count_stride = 1;
+                a.done_seq_ptr = c->m_seq; a.done_seq = ++c->seq;
                 c->scan_set ^= 1u;
                 if (c->timing) CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
                 CUDA_TRY(launch_scan_tma_qparam(a, q + (size_t)q0 * c->dim, c->sm_count, c->stream));
@@ -1386,7 +1408,8 @@ static int search_host_locked(spl_gpu_ctx *c, const spl_gpu_search_params *p, co
                 if ((rc = enqueue_fused(c, &pp, c->d_q, c->m_out, p->k, c->m_count, c->stream, c->m_total + q0))) return rc;
             }
             if (c->timing) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
-            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            if (polled && !c->timing) { if ((rc = wait_answer(c, c->seq))) return rc; }
+            else CUDA_TRY(cudaStreamSynchronize(c->stream));
             if (c->timing) {
                 float ms = 0.f;
                 CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));

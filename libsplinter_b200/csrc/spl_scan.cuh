@@ -32,6 +32,8 @@ struct ScanArgs {
     uint32_t out_stride;     //   query i writes out + i*out_stride, out_count[i*count_stride], total[i] (counters[2+i])
     uint32_t count_stride;
     uint32_t chunk_groups;   // TMA kernel: 32-slot groups handed out per work-counter increment (1..8)
+    uint32_t *done_seq_ptr;  // TMA kernel, nullable: (mapped host) word the LAST CTA sets to done_seq after every result of the
+    uint32_t done_seq;       //   launch is written -- lets the host-buffer call poll for its answer instead of synchronising the stream
     uint32_t overlap_prev;   // TMA kernel, host side only: launch so that it may start during the previous scan's tail
     // developer timeline (nullable): per CTA {start, producers done, consumers done, end} in ns
     unsigned long long *dbg;

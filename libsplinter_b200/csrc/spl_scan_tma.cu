@@ -596,6 +596,13 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
             scan_epilogue<kConsumers, false>(a, skeys + qi * qstride, sidx + qi * qstride, ws_keys, ws_idx, ws_entries, &s_flag, qi);
     }
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 3] = gtime();
+    if (a.done_seq_ptr && s_flag) {   // the last CTA, after its last result write: tell a polling host the answer is complete
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            *reinterpret_cast<volatile uint32_t *>(a.done_seq_ptr) = a.done_seq;
+        }
+    }
 }
 
 bool scan_tma_supported(uint32_t dim, uint32_t k) {
