@@ -427,6 +427,17 @@ def run_ours(args):
     if world > 1 and c5_slots and not args.skip_extra:
         c5 = c5_mixed_leg(sg, support, torch, dist, c5_slots, world, rank, local_rank, dev, tstream)
 
+    # ---- the same C4 query through the one-process group call of the C ABI (N > 1: rank 0 drives all GPUs) ----
+    group_leg = None
+    if world > 1 and not args.skip_extra:
+        m.close()
+        m = None
+        torch.cuda.empty_cache()
+        dist.barrier()
+        if rank == 0:
+            group_leg = group_call_leg(sg, support, world, k, peak)
+        dist.barrier()
+
     if rank == 0:
         gbs = job_bytes / ms_step / 1e6
         per_gpu_bytes = job_bytes / world
@@ -482,12 +493,15 @@ def run_ours(args):
             line["c4_single_gpu_anchor"] = anchor
         if c5:
             line["c5_mixed"] = c5
+        if group_leg:
+            line["group_call"] = group_leg
         if single and not args.skip_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(k, head_mask)
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
-    m.close()
+    if m is not None:
+        m.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -665,6 +679,34 @@ def c4_anchor_leg(sg, support, torch, dev, stream, peak, device_index):
                 "queries_per_s_scaled_to_2p26": round(1e3 / ms * rows / C4_ROWS, 3)}
     finally:
         m.close()
+
+
+def group_call_leg(sg, support, world, k, peak):
+    """spl_gpu_group_search: ONE process, one context per GPU over slot ranges, peer copies + device merge -- what a C host
+    calls.  Host buffers in, host buffers out (an end-to-end number), 2^22 slots per GPU, C4's query (unfiltered top-100)."""
+    rows = (1 << 22) * world
+    with sg.Group.open_dense(rows, DIM, list(range(world))) as g:
+        g.fill_synthetic(SEED_CORPUS, SEED_BLOOM)
+        q = support.synth_queries(SEED_QUERY, 8, DIM)
+        for i in range(3):
+            out, cnt = g.search(q[i], k, mode=sg.MODE_FAST)
+        t0 = time.perf_counter()
+        steps = 20
+        for i in range(steps):
+            out, cnt = g.search(q[i % 8], k, mode=sg.MODE_FAST)
+        ms = (time.perf_counter() - t0) / steps * 1e3
+        # parity: the merged hits re-scored by the oracle from regenerated rows, and sorted by the reference comparator
+        ok = int(cnt[0]) == k
+        for r in out[0][:k]:
+            sim, dist_ = _oracle_rescore(support, q[(steps - 1) % 8], r["slot_idx"])
+            ok &= abs(sim - float(r["similarity"])) <= support.TOL_SIM
+        key = np.lexsort((out[0][:k]["slot_idx"], out[0][:k]["distance"], -out[0][:k]["similarity"].astype(np.float64)))
+        ok &= bool(np.array_equal(key, np.arange(k)))
+        b = 9 * rows + 4 * DIM * int(rows * 0.999) + 4 * DIM
+        return {"workload": f"C4's query through spl_gpu_group_search: one process, {world} GPUs, {rows} slots, host buffers",
+                "slots": rows, "e2e_ms_per_query": round(ms, 4), "queries_per_s": round(1e3 / ms, 2),
+                "scanned_GB_per_s": round(b / ms / 1e6, 1), "per_gpu_frac_of_measured_hbm": round(b / ms / 1e6 / world / peak, 4),
+                "parity_ok": bool(ok)}
 
 
 def _unit_identity_violations(recs):
