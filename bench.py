@@ -434,8 +434,19 @@ def run_ours(args):
         m = None
         torch.cuda.empty_cache()
         dist.barrier()
+        torch.cuda.synchronize()
+        # The other ranks must leave their GPUs ALONE while rank 0's single process drives all of them: an NCCL barrier
+        # would park a spinning kernel on every GPU and the two processes would be time-sliced (measured: 2x slower).
+        # They wait on the rendezvous store instead -- a CPU-side wait.
+        import datetime
+        store = dist.distributed_c10d._get_default_store()
         if rank == 0:
-            group_leg = group_call_leg(sg, support, world, k, peak)
+            try:
+                group_leg = group_call_leg(sg, support, world, k, peak)
+            finally:
+                store.set("spl_group_leg_done", "1")
+        else:
+            store.wait(["spl_group_leg_done"], datetime.timedelta(seconds=900))
         dist.barrier()
 
     if rank == 0:
