@@ -130,14 +130,32 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 // (bits 7, 10), both K-major, N >> 3 at [17,23), M >> 4 at [24,29).
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 constexpr uint32_t kIdescPair = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
-// pair variant: each CTA stages its own 128 queries (16 KB) and HALF of the 256-row operand (16 KB)
-constexpr int kStagesPair = 6;
-constexpr uint32_t kStageBPair = (BN / 2) * BK * 2, kStageBytesPair = kStageA + kStageBPair;
-struct GemmSmemPair {
-    static constexpr uint32_t coef_off = kStagesPair * kStageBytesPair;
-    static constexpr uint32_t bar_off = coef_off + 2 * 2 * BN * 4;
-    static constexpr uint32_t total = bar_off + 256;
-};
+// Pair variant.  Per k-block each CTA needs its own 128 queries (16 KB) and HALF of the 256-row operand (16 KB).
+// The query operand does not change from row tile to row tile, yet streaming it with every stage made the L2 -> SM
+// traffic twice the row bytes (4.3 GB per C3 batch against 2.16 GB) and the SM's data path, not the tensor pipe, set
+// the pace (the MMA thread spent its time polling the FULL barriers).  So the first kPairResidentK k-blocks of the
+// CTA's query tile stay RESIDENT in shared memory for the whole launch (128 KB at 1024-d: half of the query; all of
+// it up to 512-d) and only the remaining k-blocks are streamed.  The ring is made of 16 KB UNITS: a k-block whose
+// query part is resident takes one unit (rows), a streamed one two (queries, rows).
+constexpr uint32_t kUnitBytes = kStageA;                    // 16 KB: 128 rows x 64 bf16, one SWIZZLE_128B operand block
+constexpr uint32_t kStageBPair = (BN / 2) * BK * 2;
+static_assert(kStageBPair == kUnitBytes, "half of the row operand is one unit");
+constexpr uint32_t kPairResidentK = 8, kPairMaxUnits = 6;
+constexpr uint32_t kPairSmemBudget = 227u * 1024u - 2048u;  // static shared memory (TMEM base word, ...) takes the rest
+struct PairLayout { uint32_t rk, units, units_off, coef_off, bar_off, total; };
+__host__ __device__ inline PairLayout pair_layout(uint32_t dim) {
+    PairLayout L;
+    const uint32_t kblocks = dim / BK;
+    L.rk = kblocks < kPairResidentK ? kblocks : kPairResidentK;
+    L.units_off = L.rk * kUnitBytes;
+    const uint32_t fixed = 2 * 2 * BN * 4 + 256;            // coefficients + barriers
+    uint32_t u = (kPairSmemBudget - L.units_off - fixed) / kUnitBytes;
+    L.units = u > kPairMaxUnits ? kPairMaxUnits : u;
+    L.coef_off = L.units_off + L.units * kUnitBytes;
+    L.bar_off = L.coef_off + 2 * 2 * BN * 4;
+    L.total = L.bar_off + 256;
+    return L;
+}
 
 }  // namespace
 
@@ -151,10 +169,11 @@ __global__ void __launch_bounds__(kThreadsGemm, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapE, const BatchArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ uint32_t s_tmem_base;
-    constexpr uint32_t NS = PAIR ? kStagesPair : kStages;
-    constexpr uint32_t STAGE = PAIR ? kStageBytesPair : kStageBytes;
-    constexpr uint32_t COEF_OFF = PAIR ? GemmSmemPair::coef_off : GemmSmem::coef_off;
-    constexpr uint32_t BAR_OFF = PAIR ? GemmSmemPair::bar_off : GemmSmem::bar_off;
+    const PairLayout PL = pair_layout(a.dim);               // (PAIR only)
+    const uint32_t NS = PAIR ? PL.units : (uint32_t)kStages;  // ring slots: 16 KB units (PAIR) or 48 KB stages
+    constexpr uint32_t STAGE = kStageBytes;                 // (1-CTA kernel)
+    const uint32_t COEF_OFF = PAIR ? PL.coef_off : GemmSmem::coef_off;
+    const uint32_t BAR_OFF = PAIR ? PL.bar_off : GemmSmem::bar_off;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = PAIR ? cluster_rank() : 0u;
     const bool leader = crank == 0;
@@ -166,6 +185,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
     auto TEMPTY = [&](uint32_t x) { return bars + 8 * (14 + x); };
     auto CFULL = [&](uint32_t x) { return bars + 8 * (16 + x); };
     auto CEMPTY = [&](uint32_t x) { return bars + 8 * (18 + x); };
+    const uint32_t QFULL = bars + 8 * 20;                    // PAIR: the resident part of the query tile has landed
     float *cA = reinterpret_cast<float *>(smem + COEF_OFF);  // [2][BN]
     float *cB = cA + 2 * BN;                                 // [2][BN]
 
@@ -173,6 +193,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
         // PAIR: the leader's FULL barrier collects its own arrive.expect_tx + the peer's remote arrive, and its
         // TEMPTY barrier the 4 epilogue warps of BOTH CTAs
         for (uint32_t s = 0; s < NS; s++) { bar_init(FULL(s), PAIR ? 2 : 1); bar_init(EMPTY(s), 1); }
+        if (PAIR) bar_init(QFULL, 2);
         for (uint32_t x = 0; x < kAcc; x++) {
             bar_init(TFULL(x), 1); bar_init(TEMPTY(x), PAIR ? 8 : 4);
             bar_init(CFULL(x), 64); bar_init(CEMPTY(x), 4);
@@ -205,46 +226,87 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
     if (warp == 0) {
         if (lane == 0 && active) {
             uint32_t st = 0, ph = 0;
+            if (PAIR) {
+                // the resident k-blocks of this CTA's query tile, once; both CTAs' bytes are counted on the leader's barrier
+                if (leader) bar_expect_tx(QFULL, 2 * PL.rk * kUnitBytes);
+                else bar_arrive_leader(QFULL);
+                for (uint32_t kb = 0; kb < PL.rk; kb++)
+                    tma_load_2d_pair(s32(smem + kb * kUnitBytes), &mapQ, QFULL, 0, (int)((qtile * kblocks + kb) * BM));
+            }
+            // PAIR: take one ring unit, wait until the MMAs that read its previous contents have retired, arm its barrier
+            // (leader: expect both CTAs' 16 KB; peer: arrive remotely) and return its shared-memory address
+            auto take_unit = [&](uint32_t &bar) -> uint32_t {
+                bar_wait(EMPTY(st), ph ^ 1u);
+                if (leader) bar_expect_tx(FULL(st), 2 * kUnitBytes);
+                else bar_arrive_leader(FULL(st));
+                bar = FULL(st);
+                const uint32_t addr = s32(smem + PL.units_off + st * kUnitBytes);
+                if (++st == NS) { st = 0; ph ^= 1u; }
+                return addr;
+            };
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 const int row0 = (int)((a.tile_first + j * a.tile_stride) * BN);
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
-                    bar_wait(EMPTY(st), ph ^ 1u);
-                    const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
-                    // both operands are stored tiled ([tile][k-block][rows][64]): each stage is one contiguous burst
+                    // both operands are stored tiled ([tile][k-block][rows][64]): each load is one contiguous burst
                     if (PAIR) {
-                        if (leader) bar_expect_tx(FULL(st), 2 * STAGE);   // both CTAs' bytes land on the leader's barrier
-                        else bar_arrive_leader(FULL(st));
-                        tma_load_2d_pair(sa, &mapQ, FULL(st), 0, (int)((qtile * kblocks + kb) * BM));
-                        tma_load_2d_pair(sb, &mapE, FULL(st), 0,
-                                         (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN + crank * (BN / 2)));
+                        uint32_t bar;
+                        if (kb >= PL.rk) {   // this k-block's queries are not resident: stream them into a unit of their own
+                            const uint32_t sa = take_unit(bar);
+                            tma_load_2d_pair(sa, &mapQ, bar, 0, (int)((qtile * kblocks + kb) * BM));
+                        }
+                        const uint32_t sb = take_unit(bar);
+                        tma_load_2d_pair(sb, &mapE, bar, 0, (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN + crank * (BN / 2)));
                     } else {
+                        bar_wait(EMPTY(st), ph ^ 1u);
+                        const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
                         bar_expect_tx(FULL(st), STAGE);
                         tma_load_2d(sa, &mapQ, FULL(st), 0, (int)((qtile * kblocks + kb) * BM));
                         tma_load_2d(sb, &mapE, FULL(st), 0, (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN));
+                        if (++st == NS) { st = 0; ph ^= 1u; }
                     }
-                    if (++st == NS) { st = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && active && leader) {
             uint32_t st = 0, ph = 0, acc = 0, aph = 0;
+            if (PAIR) { bar_wait(QFULL, 0); tc_fence_after(); }
+            // PAIR: the next ring unit, once its bytes (both CTAs') have landed; remembers its EMPTY barrier for the commit
+            auto next_unit = [&](uint32_t &empty_bar) -> uint32_t {
+                bar_wait(FULL(st), ph);
+                empty_bar = EMPTY(st);
+                const uint32_t addr = s32(smem + PL.units_off + st * kUnitBytes);
+                if (++st == NS) { st = 0; ph ^= 1u; }
+                return addr;
+            };
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 bar_wait(TEMPTY(acc), aph ^ 1u);
                 tc_fence_after();
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
-                    bar_wait(FULL(st), ph);
-                    tc_fence_after();
-                    const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
-                    const uint64_t da = make_desc(sa), db = make_desc(sb);
+                    if (PAIR) {
+                        uint32_t eq = 0, ee = 0;
+                        const bool streamed = kb >= PL.rk;
+                        const uint32_t sa = streamed ? next_unit(eq) : s32(smem + kb * kUnitBytes);
+                        const uint32_t sb = next_unit(ee);
+                        tc_fence_after();
+                        const uint64_t da = make_desc(sa), db = make_desc(sb);
 #pragma unroll
-                    for (uint32_t k = 0; k < BK / UK; k++) {
-                        if (PAIR) tc_mma_f16_pair(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdescPair, (kb | k) != 0 ? 1u : 0u);
-                        else tc_mma_f16(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+                        for (uint32_t k = 0; k < BK / UK; k++)
+                            tc_mma_f16_pair(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdescPair, (kb | k) != 0 ? 1u : 0u);
+                        // the units are free (in both CTAs of the pair) once these MMAs have read them
+                        if (streamed) tc_commit_pair(eq);
+                        tc_commit_pair(ee);
+                    } else {
+                        bar_wait(FULL(st), ph);
+                        tc_fence_after();
+                        const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
+                        const uint64_t da = make_desc(sa), db = make_desc(sb);
+#pragma unroll
+                        for (uint32_t k = 0; k < BK / UK; k++)
+                            tc_mma_f16(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+                        tc_commit(EMPTY(st));
+                        if (++st == NS) { st = 0; ph ^= 1u; }
                     }
-                    // the stage is free (in both CTAs of a pair) once these MMAs have read it
-                    if (PAIR) tc_commit_pair(EMPTY(st)); else tc_commit(EMPTY(st));
-                    if (++st == NS) { st = 0; ph ^= 1u; }
                 }
                 if (PAIR) tc_commit_pair(TFULL(acc)); else tc_commit(TFULL(acc));  // accumulator complete
                 if (++acc == kAcc) { acc = 0; aph ^= 1u; }
@@ -821,7 +883,7 @@ static bool make_map(CUtensorMap *map, const void *base, uint64_t rows, uint32_t
 cudaError_t batch_prepare() {
     cudaError_t e = cudaFuncSetAttribute(gemm_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmem::total);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmSmemPair::total);
+    e = cudaFuncSetAttribute(gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmemBudget);
     if (e != cudaSuccess) return e;
     // function attributes are per device: set here (once per context, its device current), not lazily behind a flag
     e = cudaFuncSetAttribute(select_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBatchCandCap * 12));
@@ -838,7 +900,7 @@ static cudaError_t launch_gemm(const CUtensorMap &mapQ, const CUtensorMap &mapE,
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kThreadsGemm);
-    cfg.dynamicSmemBytes = GemmSmemPair::total;
+    cfg.dynamicSmemBytes = pair_layout(a.dim).total;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
