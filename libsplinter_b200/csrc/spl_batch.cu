@@ -130,30 +130,31 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 // (bits 7, 10), both K-major, N >> 3 at [17,23), M >> 4 at [24,29).
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 constexpr uint32_t kIdescPair = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
-// Pair variant.  Per k-block each CTA needs its own 128 queries (16 KB) and HALF of the 256-row operand (16 KB).
-// The query operand does not change from row tile to row tile, yet streaming it with every stage made the L2 -> SM
-// traffic twice the row bytes (4.3 GB per C3 batch against 2.16 GB) and the SM's data path, not the tensor pipe, set
-// the pace (the MMA thread spent its time polling the FULL barriers).  So the first kPairResidentK k-blocks of the
-// CTA's query tile stay RESIDENT in shared memory for the whole launch (128 KB at 1024-d: half of the query; all of
-// it up to 512-d) and only the remaining k-blocks are streamed.  The ring is made of 16 KB UNITS: a k-block whose
-// query part is resident takes one unit (rows), a streamed one two (queries, rows).
+// Pair variant.  Per k-block each CTA needs its own 128 queries (16 KB, always an L2 hit: the whole query operand is
+// 512 KB) and HALF of the 256-row operand (16 KB, always from HBM).  What paces the main loop is how many ROW bytes
+// are in flight per SM: the MMA thread spends its waiting time on the FULL barrier of the row operand, and the one
+// experiment that traded ring depth for less L2 traffic (keeping half of the query tile resident: L2 -> SM bytes
+// 4.3 -> 3.2 GB, but only 5 units of 16 KB left for the ring) made the launch SLOWER (420 -> 494 us).  So the two
+// operands get rings of their own, sized by their latencies: a shallow one for the queries (L2 latency, 3 units)
+// and everything else for the rows (HBM latency under load, 10 units = 160 KB per SM against 96 KB before).
 constexpr uint32_t kUnitBytes = kStageA;                    // 16 KB: 128 rows x 64 bf16, one SWIZZLE_128B operand block
 constexpr uint32_t kStageBPair = (BN / 2) * BK * 2;
 static_assert(kStageBPair == kUnitBytes, "half of the row operand is one unit");
-constexpr uint32_t kPairResidentK = 8, kPairMaxUnits = 6;
+constexpr uint32_t kPairQUnits = 3, kPairEUnitsMax = 10;
+constexpr uint32_t kPairBarBytes = 512;                     // 2 x 13 ring barriers + 9 others
 constexpr uint32_t kPairSmemBudget = 227u * 1024u - 2048u;  // static shared memory (TMEM base word, ...) takes the rest
-struct PairLayout { uint32_t rk, units, units_off, coef_off, bar_off, total; };
+struct PairLayout { uint32_t q_units, e_units, e_off, coef_off, bar_off, total; };
 __host__ __device__ inline PairLayout pair_layout(uint32_t dim) {
+    (void)dim;
     PairLayout L;
-    const uint32_t kblocks = dim / BK;
-    L.rk = kblocks < kPairResidentK ? kblocks : kPairResidentK;
-    L.units_off = L.rk * kUnitBytes;
-    const uint32_t fixed = 2 * 2 * BN * 4 + 256;            // coefficients + barriers
-    uint32_t u = (kPairSmemBudget - L.units_off - fixed) / kUnitBytes;
-    L.units = u > kPairMaxUnits ? kPairMaxUnits : u;
-    L.coef_off = L.units_off + L.units * kUnitBytes;
+    L.q_units = kPairQUnits;
+    L.e_off = L.q_units * kUnitBytes;
+    const uint32_t fixed = 2 * 2 * BN * 4 + kPairBarBytes;  // coefficients + barriers
+    const uint32_t u = (kPairSmemBudget - L.e_off - fixed) / kUnitBytes;
+    L.e_units = u > kPairEUnitsMax ? kPairEUnitsMax : u;
+    L.coef_off = L.e_off + L.e_units * kUnitBytes;
     L.bar_off = L.coef_off + 2 * 2 * BN * 4;
-    L.total = L.bar_off + 256;
+    L.total = L.bar_off + kPairBarBytes;
     return L;
 }
 
@@ -170,30 +171,38 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ uint32_t s_tmem_base;
     const PairLayout PL = pair_layout(a.dim);               // (PAIR only)
-    const uint32_t NS = PAIR ? PL.units : (uint32_t)kStages;  // ring slots: 16 KB units (PAIR) or 48 KB stages
-    constexpr uint32_t STAGE = kStageBytes;                 // (1-CTA kernel)
+    constexpr uint32_t NS = kStages, STAGE = kStageBytes;   // (1-CTA kernel: 48 KB stages holding both operands)
+    const uint32_t NQU = PL.q_units, NEU = PL.e_units;      // (PAIR: separate rings of 16 KB units)
     const uint32_t COEF_OFF = PAIR ? PL.coef_off : GemmSmem::coef_off;
     const uint32_t BAR_OFF = PAIR ? PL.bar_off : GemmSmem::bar_off;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = PAIR ? cluster_rank() : 0u;
     const bool leader = crank == 0;
     const uint32_t bars = s32(smem + BAR_OFF);
-    // barrier map: full[s] 0..5, empty[s] 6..11, tfull[a] 12..13, tempty[a] 14..15, cfull[c] 16..17, cempty[c] 18..19
+    // barrier map: full[s] 0..5, empty[s] 6..11, tfull[a] 12..13, tempty[a] 14..15, cfull[c] 16..17, cempty[c] 18..19;
+    // PAIR: query ring full 20..22 / empty 23..25, row ring full 26..35 / empty 36..45
     auto FULL = [&](uint32_t s) { return bars + 8 * s; };
     auto EMPTY = [&](uint32_t s) { return bars + 8 * (6 + s); };
     auto TFULL = [&](uint32_t x) { return bars + 8 * (12 + x); };
     auto TEMPTY = [&](uint32_t x) { return bars + 8 * (14 + x); };
     auto CFULL = [&](uint32_t x) { return bars + 8 * (16 + x); };
     auto CEMPTY = [&](uint32_t x) { return bars + 8 * (18 + x); };
-    const uint32_t QFULL = bars + 8 * 20;                    // PAIR: the resident part of the query tile has landed
+    auto QFULLB = [&](uint32_t u) { return bars + 8 * (20 + u); };
+    auto QEMPTYB = [&](uint32_t u) { return bars + 8 * (23 + u); };
+    auto EFULLB = [&](uint32_t u) { return bars + 8 * (26 + u); };
+    auto EEMPTYB = [&](uint32_t u) { return bars + 8 * (36 + u); };
     float *cA = reinterpret_cast<float *>(smem + COEF_OFF);  // [2][BN]
     float *cB = cA + 2 * BN;                                 // [2][BN]
 
     if (threadIdx.x == 0) {
         // PAIR: the leader's FULL barrier collects its own arrive.expect_tx + the peer's remote arrive, and its
         // TEMPTY barrier the 4 epilogue warps of BOTH CTAs
-        for (uint32_t s = 0; s < NS; s++) { bar_init(FULL(s), PAIR ? 2 : 1); bar_init(EMPTY(s), 1); }
-        if (PAIR) bar_init(QFULL, 2);
+        if (PAIR) {
+            for (uint32_t u = 0; u < NQU; u++) { bar_init(QFULLB(u), 2); bar_init(QEMPTYB(u), 1); }
+            for (uint32_t u = 0; u < NEU; u++) { bar_init(EFULLB(u), 2); bar_init(EEMPTYB(u), 1); }
+        } else {
+            for (uint32_t s = 0; s < NS; s++) { bar_init(FULL(s), 1); bar_init(EMPTY(s), 1); }
+        }
         for (uint32_t x = 0; x < kAcc; x++) {
             bar_init(TFULL(x), 1); bar_init(TEMPTY(x), PAIR ? 8 : 4);
             bar_init(CFULL(x), 64); bar_init(CEMPTY(x), 4);
@@ -225,37 +234,24 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
 
     if (warp == 0) {
         if (lane == 0 && active) {
-            uint32_t st = 0, ph = 0;
-            if (PAIR) {
-                // the resident k-blocks of this CTA's query tile, once; both CTAs' bytes are counted on the leader's barrier
-                if (leader) bar_expect_tx(QFULL, 2 * PL.rk * kUnitBytes);
-                else bar_arrive_leader(QFULL);
-                for (uint32_t kb = 0; kb < PL.rk; kb++)
-                    tma_load_2d_pair(s32(smem + kb * kUnitBytes), &mapQ, QFULL, 0, (int)((qtile * kblocks + kb) * BM));
-            }
-            // PAIR: take one ring unit, wait until the MMAs that read its previous contents have retired, arm its barrier
-            // (leader: expect both CTAs' 16 KB; peer: arrive remotely) and return its shared-memory address
-            auto take_unit = [&](uint32_t &bar) -> uint32_t {
-                bar_wait(EMPTY(st), ph ^ 1u);
-                if (leader) bar_expect_tx(FULL(st), 2 * kUnitBytes);
-                else bar_arrive_leader(FULL(st));
-                bar = FULL(st);
-                const uint32_t addr = s32(smem + PL.units_off + st * kUnitBytes);
-                if (++st == NS) { st = 0; ph ^= 1u; }
-                return addr;
-            };
+            uint32_t st = 0, ph = 0, qu = 0, qph = 0, eu = 0, eph = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 const int row0 = (int)((a.tile_first + j * a.tile_stride) * BN);
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
                     // both operands are stored tiled ([tile][k-block][rows][64]): each load is one contiguous burst
                     if (PAIR) {
-                        uint32_t bar;
-                        if (kb >= PL.rk) {   // this k-block's queries are not resident: stream them into a unit of their own
-                            const uint32_t sa = take_unit(bar);
-                            tma_load_2d_pair(sa, &mapQ, bar, 0, (int)((qtile * kblocks + kb) * BM));
-                        }
-                        const uint32_t sb = take_unit(bar);
-                        tma_load_2d_pair(sb, &mapE, bar, 0, (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN + crank * (BN / 2)));
+                        // Each ring unit: wait until the MMAs that read its previous contents have retired, arm its barrier
+                        // (leader: expect both CTAs' 16 KB; peer: arrive remotely), load.  The row operand first: it is
+                        // the one that comes from HBM.
+                        bar_wait(EEMPTYB(eu), eph ^ 1u);
+                        if (leader) bar_expect_tx(EFULLB(eu), 2 * kUnitBytes); else bar_arrive_leader(EFULLB(eu));
+                        tma_load_2d_pair(s32(smem + PL.e_off + eu * kUnitBytes), &mapE, EFULLB(eu), 0,
+                                         (int)((((uint32_t)row0 / BN) * kblocks + kb) * BN + crank * (BN / 2)));
+                        if (++eu == NEU) { eu = 0; eph ^= 1u; }
+                        bar_wait(QEMPTYB(qu), qph ^ 1u);
+                        if (leader) bar_expect_tx(QFULLB(qu), 2 * kUnitBytes); else bar_arrive_leader(QFULLB(qu));
+                        tma_load_2d_pair(s32(smem + qu * kUnitBytes), &mapQ, QFULLB(qu), 0, (int)((qtile * kblocks + kb) * BM));
+                        if (++qu == NQU) { qu = 0; qph ^= 1u; }
                     } else {
                         bar_wait(EMPTY(st), ph ^ 1u);
                         const uint32_t sa = s32(smem + st * STAGE), sb = sa + kStageA;
@@ -269,33 +265,24 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
         }
     } else if (warp == 1) {
         if (lane == 0 && active && leader) {
-            uint32_t st = 0, ph = 0, acc = 0, aph = 0;
-            if (PAIR) { bar_wait(QFULL, 0); tc_fence_after(); }
-            // PAIR: the next ring unit, once its bytes (both CTAs') have landed; remembers its EMPTY barrier for the commit
-            auto next_unit = [&](uint32_t &empty_bar) -> uint32_t {
-                bar_wait(FULL(st), ph);
-                empty_bar = EMPTY(st);
-                const uint32_t addr = s32(smem + PL.units_off + st * kUnitBytes);
-                if (++st == NS) { st = 0; ph ^= 1u; }
-                return addr;
-            };
+            uint32_t st = 0, ph = 0, acc = 0, aph = 0, qu = 0, qph = 0, eu = 0, eph = 0;
             for (uint32_t j = group; j < a.n_tiles; j += ngroups) {
                 bar_wait(TEMPTY(acc), aph ^ 1u);
                 tc_fence_after();
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
                     if (PAIR) {
-                        uint32_t eq = 0, ee = 0;
-                        const bool streamed = kb >= PL.rk;
-                        const uint32_t sa = streamed ? next_unit(eq) : s32(smem + kb * kUnitBytes);
-                        const uint32_t sb = next_unit(ee);
+                        bar_wait(QFULLB(qu), qph);
+                        bar_wait(EFULLB(eu), eph);
                         tc_fence_after();
-                        const uint64_t da = make_desc(sa), db = make_desc(sb);
+                        const uint64_t da = make_desc(s32(smem + qu * kUnitBytes)), db = make_desc(s32(smem + PL.e_off + eu * kUnitBytes));
 #pragma unroll
                         for (uint32_t k = 0; k < BK / UK; k++)
                             tc_mma_f16_pair(tmem_base + acc * BN, da + 2 * k, db + 2 * k, kIdescPair, (kb | k) != 0 ? 1u : 0u);
                         // the units are free (in both CTAs of the pair) once these MMAs have read them
-                        if (streamed) tc_commit_pair(eq);
-                        tc_commit_pair(ee);
+                        tc_commit_pair(QEMPTYB(qu));
+                        tc_commit_pair(EEMPTYB(eu));
+                        if (++qu == NQU) { qu = 0; qph ^= 1u; }
+                        if (++eu == NEU) { eu = 0; eph ^= 1u; }
                     } else {
                         bar_wait(FULL(st), ph);
                         tc_fence_after();
