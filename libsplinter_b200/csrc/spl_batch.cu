@@ -131,23 +131,26 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 constexpr uint32_t kIdescPair = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
 // Pair variant.  Per k-block each CTA needs its own 128 queries (16 KB, always an L2 hit: the whole query operand is
-// 512 KB) and HALF of the 256-row operand (16 KB, always from HBM).  What paces the main loop is how many ROW bytes
-// are in flight per SM: the MMA thread spends its waiting time on the FULL barrier of the row operand, and the one
-// experiment that traded ring depth for less L2 traffic (keeping half of the query tile resident: L2 -> SM bytes
-// 4.3 -> 3.2 GB, but only 5 units of 16 KB left for the ring) made the launch SLOWER (420 -> 494 us).  So the two
-// operands get rings of their own, sized by their latencies: a shallow one for the queries (L2 latency, 3 units)
-// and everything else for the rows (HBM latency under load, 10 units = 160 KB per SM against 96 KB before).
+// 512 KB) and HALF of the 256-row operand (16 KB, from HBM).  The two operands get rings of their own, made of 16 KB
+// units.  What was measured while looking for the main loop's limiter (C3: 256 x 2^20 x 1024, pass 2 = 420 us):
+//   * re-fetching the query tile for every row tile doubles the L2 -> SM bytes (4.3 GB against 2.16 GB of rows), but
+//     it is NOT what paces the loop: a probe that skipped the query loads after the first tile (wrong results, same
+//     MMAs) ran only 2.5 % faster (0.480 -> 0.468 ms per batch);
+//   * keeping half of the query tile resident in shared memory (L2 -> SM 3.2 GB, but only 5 units left for the ring)
+//     was SLOWER (494 us): ring depth matters more than those bytes;
+//   * ring shapes beyond 4 query units + the rest for rows change nothing (query units 2 / 3 / 4 / 5 / 6: 0.551 /
+//     0.499 / 0.490 / 0.490 / 0.490 ms per batch).
+// The launch runs at 1.30-1.35 PFLOP/s at a power-capped 1.42 GHz -- 93-96 % of what cuBLAS sustains under the same cap.
 constexpr uint32_t kUnitBytes = kStageA;                    // 16 KB: 128 rows x 64 bf16, one SWIZZLE_128B operand block
 constexpr uint32_t kStageBPair = (BN / 2) * BK * 2;
 static_assert(kStageBPair == kUnitBytes, "half of the row operand is one unit");
-constexpr uint32_t kPairQUnits = 3, kPairEUnitsMax = 10;
-constexpr uint32_t kPairBarBytes = 512;                     // 2 x 13 ring barriers + 9 others
+constexpr uint32_t kPairQUnits = 4, kPairEUnitsMax = 11;
+constexpr uint32_t kPairBarBytes = 512;                     // up to 56 barriers
 constexpr uint32_t kPairSmemBudget = 227u * 1024u - 2048u;  // static shared memory (TMEM base word, ...) takes the rest
 struct PairLayout { uint32_t q_units, e_units, e_off, coef_off, bar_off, total; };
-__host__ __device__ inline PairLayout pair_layout(uint32_t dim) {
-    (void)dim;
+__host__ __device__ inline PairLayout pair_layout(uint32_t q_units_req) {
     PairLayout L;
-    L.q_units = kPairQUnits;
+    L.q_units = q_units_req >= 2 && q_units_req <= 6 ? q_units_req : kPairQUnits;
     L.e_off = L.q_units * kUnitBytes;
     const uint32_t fixed = 2 * 2 * BN * 4 + kPairBarBytes;  // coefficients + barriers
     const uint32_t u = (kPairSmemBudget - L.e_off - fixed) / kUnitBytes;
@@ -170,7 +173,7 @@ __global__ void __launch_bounds__(kThreadsGemm, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapE, const BatchArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ uint32_t s_tmem_base;
-    const PairLayout PL = pair_layout(a.dim);               // (PAIR only)
+    const PairLayout PL = pair_layout(a.pair_q_units);      // (PAIR only)
     constexpr uint32_t NS = kStages, STAGE = kStageBytes;   // (1-CTA kernel: 48 KB stages holding both operands)
     const uint32_t NQU = PL.q_units, NEU = PL.e_units;      // (PAIR: separate rings of 16 KB units)
     const uint32_t COEF_OFF = PAIR ? PL.coef_off : GemmSmem::coef_off;
@@ -180,7 +183,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
     const bool leader = crank == 0;
     const uint32_t bars = s32(smem + BAR_OFF);
     // barrier map: full[s] 0..5, empty[s] 6..11, tfull[a] 12..13, tempty[a] 14..15, cfull[c] 16..17, cempty[c] 18..19;
-    // PAIR: query ring full 20..22 / empty 23..25, row ring full 26..35 / empty 36..45
+    // PAIR: query ring full 20..25 / empty 26..31, row ring full 32..43 / empty 44..55
     auto FULL = [&](uint32_t s) { return bars + 8 * s; };
     auto EMPTY = [&](uint32_t s) { return bars + 8 * (6 + s); };
     auto TFULL = [&](uint32_t x) { return bars + 8 * (12 + x); };
@@ -188,9 +191,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant
     auto CFULL = [&](uint32_t x) { return bars + 8 * (16 + x); };
     auto CEMPTY = [&](uint32_t x) { return bars + 8 * (18 + x); };
     auto QFULLB = [&](uint32_t u) { return bars + 8 * (20 + u); };
-    auto QEMPTYB = [&](uint32_t u) { return bars + 8 * (23 + u); };
-    auto EFULLB = [&](uint32_t u) { return bars + 8 * (26 + u); };
-    auto EEMPTYB = [&](uint32_t u) { return bars + 8 * (36 + u); };
+    auto QEMPTYB = [&](uint32_t u) { return bars + 8 * (26 + u); };
+    auto EFULLB = [&](uint32_t u) { return bars + 8 * (32 + u); };
+    auto EEMPTYB = [&](uint32_t u) { return bars + 8 * (44 + u); };
     float *cA = reinterpret_cast<float *>(smem + COEF_OFF);  // [2][BN]
     float *cB = cA + 2 * BN;                                 // [2][BN]
 
@@ -887,7 +890,7 @@ static cudaError_t launch_gemm(const CUtensorMap &mapQ, const CUtensorMap &mapE,
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kThreadsGemm);
-    cfg.dynamicSmemBytes = pair_layout(a.dim).total;
+    cfg.dynamicSmemBytes = pair_layout(a.pair_q_units).total;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -945,6 +948,10 @@ cudaError_t batch_search(const BatchArgs &base, const BatchScratchLayout &L, uns
     const uint64_t n_pad = ((uint64_t)a.n + BN - 1) / BN * BN;
     // 256 queries and up run on CTA pairs (cta_group::2); the row operand is then fetched in two 128-row halves
     const bool pair = a.n_qtiles % 2 == 0 && getenv("SPL_GPU_BATCH_1CTA") == nullptr;
+    {   // developer knob: depth of the query ring of the pair kernel (the row ring takes the rest)
+        const char *qu = getenv("SPL_GPU_PAIR_QUNITS");
+        a.pair_q_units = qu ? (uint32_t)atoi(qu) : 0u;
+    }
     if (!make_map(&mapQ, q16, a.nq_pad, a.dim, BM) || !make_map(&mapE, a.E16, n_pad, a.dim, pair ? BN / 2 : BN))
         return cudaErrorNotSupported;
 

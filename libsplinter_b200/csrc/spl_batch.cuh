@@ -29,6 +29,7 @@ struct BatchArgs {
                                   // Rows failing it are the tail of the sorted result, so it is applied after the re-score.
     // schedule
     uint32_t pass;                // 1: per-tile minima, 2: append below threshold
+    uint32_t pair_q_units;        // pair kernel: depth of the query ring in 16 KB units (0 = default)
     uint32_t tile_first, tile_stride, n_tiles;
     // scratch
     float *thr;                   // [nq_pad]   bound on t ...
