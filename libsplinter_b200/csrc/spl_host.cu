@@ -1246,7 +1246,9 @@ static int wait_answer(spl_gpu_ctx *c, uint32_t expect) {
     for (uint32_t spins = 0;; spins++) {
         if (__atomic_load_n(c->h_seq, __ATOMIC_ACQUIRE) == expect) return 0;
         if ((spins & 1023u) == 1023u && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20)) break;
+#if defined(__x86_64__) || defined(__i386__)
         __builtin_ia32_pause();
+#endif
     }
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     return 0;
