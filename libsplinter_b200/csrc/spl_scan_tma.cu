@@ -169,6 +169,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint32_t s_flag;
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
+    __shared__ uint32_t s_dense;  // small-batch consumers: the producers see most slots pass (see the lazy loop body)
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const TmaLayout L = tma_layout(a.dim, a.k, NQ, QP);
     const uint32_t list_entries = L.list_entries;
@@ -182,6 +183,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     if (threadIdx.x == 0) {
         if (a.dbg) a.dbg[blockIdx.x * 8 + 0] = gtime();
         s_seq = 0;
+        s_dense = 0;
         for (uint32_t s = 0; s < NP; s++) { mbar_init(full0 + 8 * s, 2); publish_gen(empty0 + 8 * s, 0); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -275,6 +277,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                 const uint32_t len = c & 15u;
                 const uint32_t pick = T * 10u >= 260u * len ? 1u : (T * 10u >= 130u * len ? 2u : (T * 10u >= 16u * len ? 4u : 8u));
                 want = pick < cg ? pick : cg;
+                if (NQ > 1 && lane == 0) s_dense = T * 10u >= 130u * len ? 1u : 0u;   // >= 40 % of the slots pass
             }
             if (T == 0) return;
             __syncwarp();  // clist writes -> reads by other lanes
@@ -456,6 +459,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
         const bool thresholds = a.min_sim > 0.f || a.max_dist > 0.f;
         uint4 *my_state = wstate + my_q * kConsumers + warp;
         uint32_t nsurv = 0;  // survivors of this lane's query
+        const bool lazy_ok = a.order == SPL_ORDER_COSINE && !(a.max_dist > 0.f) && !a.keys_out;
         auto tsum = [&](auto &v, auto n_tag) -> float {      // transposed warp sum of v[N]
             constexpr int N = decltype(n_tag)::value;
             uint32_t width = 16;
@@ -496,6 +500,94 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
 #pragma unroll
             for (int j = 0; j < V; j++) { norm4(x[j], pe0); norm4(y[j], pe1); }
             float ev[2] = { pe0.x + pe0.y, pe1.x + pe1.y };
+            if (lazy_ok && *reinterpret_cast<volatile uint32_t *>(&s_dense)) {
+                // ---- lazy body: where most slots pass, the lists are warm and almost no candidate is admitted.  In the
+                // reference's order (similarity first) the distance then only matters for the few that are: score the
+                // dot products alone (a third of the FMAs, half of the reduction), test the similarity against the
+                // list's bound, and compute sum (q-e)^2 -- same per-lane order, same butterfly, hence the same bits as
+                // the full body -- only for a candidate whose similarity does not already rule it out.
+                constexpr int NVL = 2 * NQ;          // value index = query * 2 + row
+                constexpr uint32_t TBL = 32 / NVL;   // lane L ends up holding value L / TBL
+                float accl[NVL];
+#pragma unroll
+                for (int qi = 0; qi < NQ; qi++) {
+                    const float4 *qrow = sq4 + qi * qstride4;
+                    float2 pd0 = make_float2(0.f, 0.f), pd1 = pd0;
+#pragma unroll
+                    for (int j = 0; j < V; j++) {
+                        const float4 qv = qrow[32 * j];
+                        pd0 = fma2(lo2(qv), lo2(x[j]), pd0); pd0 = fma2(hi2(qv), hi2(x[j]), pd0);
+                        pd1 = fma2(lo2(qv), lo2(y[j]), pd1); pd1 = fma2(hi2(qv), hi2(y[j]), pd1);
+                    }
+                    accl[qi * 2 + 0] = pd0.x + pd0.y; accl[qi * 2 + 1] = pd1.x + pd1.y;
+                }
+                const float etot = tsum(ev, std::integral_constant<int, 2>{});
+                const float dotl = tsum(accl, std::integral_constant<int, NVL>{});
+                const uint32_t lq = lane / (2 * TBL), lr = (lane / TBL) & 1u;
+                const bool lactive = (lane % TBL) == 0;          // one lane per (query, row)
+                const float mbl = __shfl_sync(0xffffffffu, etot, lr << 4);
+                const uint32_t rowl = lr ? mt.z : mt.x, fl = lr ? mt.w : mt.y;
+                bool passl = lactive && (lr == 0 || two);
+                float siml = 0.f;
+                if (fl & SPL_ROW_EMB) {
+                    siml = cosine_from_sums(dotl, smaq[lq], mbl);
+                    if (a.min_sim > 0.f && siml < a.min_sim) passl = false;
+                } else if (a.min_sim > 0.f) {   // _search.c:388-393
+                    passl = false;
+                }
+                static_assert(2 * TBL == 4 * TB, "both bodies give a query the same group of lanes");
+                nsurv += __popc(__ballot_sync(0xffffffffu, passl) & group_mask);
+                const uint4 stl = *(wstate + lq * kConsumers + warp);
+                // similarity alone decides unless it ties with the bound's: ~ord(sim) is the key's high word
+                const uint32_t hil = ~f2ord(siml);
+                const bool admitl = passl && ((stl.w & 0xffffu) < a.k || hil <= stl.y);
+                unsigned ml = __ballot_sync(0xffffffffu, admitl);
+                while (ml) {   // warp-uniform
+                    const int l = __ffs(ml) - 1;
+                    ml &= ml - 1;
+                    const uint32_t cq = (uint32_t)l / (2 * TBL), cr = ((uint32_t)l / TBL) & 1u;
+                    const uint32_t crow = __shfl_sync(0xffffffffu, rowl, l);
+                    const uint32_t cf = __shfl_sync(0xffffffffu, fl, l);
+                    const float csim = __shfl_sync(0xffffffffu, siml, l);
+                    float cdist = FLT_MAX;
+                    if (cf & SPL_ROW_EMB) {
+                        const float4 *qrow = sq4 + cq * qstride4;
+                        float2 ps = make_float2(0.f, 0.f);
+                        if (cr) {
+#pragma unroll
+                            for (int j = 0; j < V; j++) {
+                                const float4 qv = qrow[32 * j];
+                                float2 t = sub2(lo2(qv), lo2(y[j])); ps = fma2(t, t, ps);
+                                t = sub2(hi2(qv), hi2(y[j])); ps = fma2(t, t, ps);
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < V; j++) {
+                                const float4 qv = qrow[32 * j];
+                                float2 t = sub2(lo2(qv), lo2(x[j])); ps = fma2(t, t, ps);
+                                t = sub2(hi2(qv), hi2(x[j])); ps = fma2(t, t, ps);
+                            }
+                        }
+                        float ssum = ps.x + ps.y;
+#pragma unroll
+                        for (int off = 16; off > 0; off >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, off);
+                        cdist = __fsqrt_rn(ssum);
+                    }
+                    const uint64_t ckey = make_key(a.order, csim, cdist);
+                    uint4 *stp = wstate + cq * kConsumers + warp;
+                    const uint4 cs = *stp;
+                    WarpTopK T;
+                    T.keys = skeys + cq * qstride + warp * a.k; T.idxs = sidx + cq * qstride + warp * a.k;
+                    T.k = a.k; T.cnt = cs.w & 0xffffu; T.thr_pos = cs.w >> 16;
+                    T.thr_key = ((uint64_t)cs.y << 32) | cs.x; T.thr_idx = cs.z;
+                    if (T.admits(ckey, crow)) {
+                        T.insert(ckey, crow, lane);
+                        if (lane == 0) *stp = make_uint4((uint32_t)T.thr_key, (uint32_t)(T.thr_key >> 32), T.thr_idx, (T.thr_pos << 16) | T.cnt);
+                    }
+                    __syncwarp();
+                }
+                continue;
+            }
             float acc[NV];
 #pragma unroll
             for (int qi = 0; qi < NQ; qi++) {
