@@ -170,6 +170,10 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     __shared__ uint32_t s_flag;
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
     __shared__ uint32_t s_dense;  // small-batch consumers: the producers see most slots pass (see the lazy loop body)
+    // consumers with the query in shared memory: the k smallest primary key words (the key's high half: similarity in cosine order, distance
+    // in L2 order) any warp of this CTA has offered to its list so far, per query, and the largest of them (see cta_note)
+    __shared__ uint32_t s_cta_hi[tma_query_in_smem(V * 128, NQ) ? NQ * 256 : 1];   // k <= 256
+    __shared__ uint32_t s_cta_kth[4];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const TmaLayout L = tma_layout(a.dim, a.k, NQ, QP);
     const uint32_t list_entries = L.list_entries;
@@ -195,6 +199,8 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
             wstate[i] = make_uint4((uint32_t)kKeySentinel, (uint32_t)(kKeySentinel >> 32), kIdxSentinel, 0u);
             reinterpret_cast<uint32_t *>(wstate + NQ * kConsumers)[i] = 0u;
         }
+        for (uint32_t i = threadIdx.x; i < NQ * 256; i += blockDim.x) s_cta_hi[i] = 0xffffffffu;
+        if (threadIdx.x < 4) s_cta_kth[threadIdx.x] = 0xffffffffu;
         float4 *sq4 = reinterpret_cast<float4 *>(smem + L.q_off);
         const float4 *gq4 = reinterpret_cast<const float4 *>(a.q);
         for (uint32_t i = threadIdx.x; i < NQ * (a.dim >> 2); i += blockDim.x) sq4[i] = gq4[i];
@@ -477,6 +483,30 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
             for (; width > 0; width >>= 1) r += __shfl_xor_sync(0xffffffffu, r, width);
             return r;
         };
+        // ---- a CTA-wide admission bound on the key's primary word ---------------------------------------------------
+        // A warp sees a sixteenth of the CTA's rows; its own list's k-th key is a loose bound (with a selective mask a
+        // warp meets a few dozen rows per query and admits every other one).  So the CTA also keeps, per query, the k
+        // smallest PRIMARY words (32 bits: one CAS) of the rows its warps have admitted, lock-free: a row whose primary
+        // word is larger than the largest of those k has k rows of this CTA strictly ahead of it and cannot be in the
+        // answer, whatever its warp's list looks like.  Words only ever shrink, so a stale read is a looser bound, never a
+        // wrong one; ties on the word are let through to the exact 96-bit comparison of the warp's list.
+        auto cta_note = [&](uint32_t cq, uint32_t hi) __attribute__((always_inline)) {   // warp-uniform arguments
+            volatile uint32_t *sl = s_cta_hi + cq * a.k;
+            for (;;) {
+                uint32_t mx = 0, mp = 0;
+                for (uint32_t p = lane; p < a.k; p += kWarp) { const uint32_t v = sl[p]; if (v >= mx) { mx = v; mp = p; } }
+                const uint32_t wmx = __reduce_max_sync(0xffffffffu, mx);
+                if (hi >= wmx) {   // nothing (more) to replace: wmx bounds the k-th smallest word from above
+                    if (lane == 0) atomicMin(&s_cta_kth[cq], wmx);
+                    break;
+                }
+                const unsigned who = __ballot_sync(0xffffffffu, lane < a.k && mx == wmx);
+                const uint32_t pos = __shfl_sync(0xffffffffu, mp, __ffs(who) - 1);
+                uint32_t ok = 0;
+                if (lane == 0) ok = atomicCAS(&s_cta_hi[cq * a.k + pos], wmx, hi) == wmx;
+                if (__shfl_sync(0xffffffffu, ok, 0)) hi = 0xffffffffu;   // placed: one more pass publishes the new maximum
+            }
+        };
         uint32_t slot = warp, gen = 0;
         if (slot >= NP) { slot -= NP; gen++; }
         for (;;) {
@@ -540,7 +570,8 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                 const uint4 stl = *(wstate + lq * kConsumers + warp);
                 // similarity alone decides unless it ties with the bound's: ~ord(sim) is the key's high word
                 const uint32_t hil = ~f2ord(siml);
-                const bool admitl = passl && ((stl.w & 0xffffu) < a.k || hil <= stl.y);
+                const bool admitl = passl && hil <= *reinterpret_cast<volatile uint32_t *>(&s_cta_kth[lq]) &&
+                                    ((stl.w & 0xffffu) < a.k || hil <= stl.y);
                 unsigned ml = __ballot_sync(0xffffffffu, admitl);
                 while (ml) {   // warp-uniform
                     const int l = __ffs(ml) - 1;
@@ -549,6 +580,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                     const uint32_t crow = __shfl_sync(0xffffffffu, rowl, l);
                     const uint32_t cf = __shfl_sync(0xffffffffu, fl, l);
                     const float csim = __shfl_sync(0xffffffffu, siml, l);
+                    cta_note(cq, ~f2ord(csim));
                     float cdist = FLT_MAX;
                     if (cf & SPL_ROW_EMB) {
                         const float4 *qrow = sq4 + cq * qstride4;
@@ -626,7 +658,8 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                 continue;
             }
             const uint4 st = *my_state;
-            const bool admit = pass && ((st.w & 0xffffu) < a.k || better(key, row, ((uint64_t)st.y << 32) | st.x, st.z));
+            const bool admit = pass && (uint32_t)(key >> 32) <= *reinterpret_cast<volatile uint32_t *>(&s_cta_kth[my_q]) &&
+                               ((st.w & 0xffffu) < a.k || better(key, row, ((uint64_t)st.y << 32) | st.x, st.z));
             unsigned m = __ballot_sync(0xffffffffu, admit);
             while (m) {   // warp-uniform
                 const int l = __ffs(m) - 1;
@@ -634,6 +667,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                 const uint64_t ckey = __shfl_sync(0xffffffffu, key, l);
                 const uint32_t crow = __shfl_sync(0xffffffffu, row, l);
                 const uint32_t cq = (uint32_t)l / (4 * TB);
+                cta_note(cq, (uint32_t)(ckey >> 32));
                 uint4 *stp = wstate + cq * kConsumers + warp;
                 const uint4 cs = *stp;   // re-read: an earlier candidate of this pair may have moved the bound
                 WarpTopK T;
