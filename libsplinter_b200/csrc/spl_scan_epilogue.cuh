@@ -211,13 +211,15 @@ __device__ __forceinline__ void warp_merge32_rolled(uint64_t &key, uint32_t &idx
 }
 // tree merge of the sorted lists of warps 0..nw-1 through xk/xi; afterwards warp 0 holds the CTA's best 32.
 // Called by ALL threads of the CTA.
-static __device__ __noinline__ KeyIdx cta_tree_merge32_shared(KeyIdx v, uint64_t *xk, uint32_t *xi, uint32_t nw) {
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// `group` (a power of two dividing nw): the warps merge in independent groups of that many -- afterwards the first warp
+// of every group holds its group's best 32 (group = nw: one tree over all warps).
+static __device__ __noinline__ KeyIdx cta_tree_merge32_shared(KeyIdx v, uint64_t *xk, uint32_t *xi, uint32_t nw, uint32_t group) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wg = warp & (group - 1);
 #pragma unroll 1
-    for (uint32_t step = 1; step < nw; step <<= 1) {
-        if (warp < nw && (warp & (2 * step - 1)) == step) { xk[warp * 32 + lane] = v.key; xi[warp * 32 + lane] = v.idx; }
+    for (uint32_t step = 1; step < group; step <<= 1) {
+        if (warp < nw && (wg & (2 * step - 1)) == step) { xk[warp * 32 + lane] = v.key; xi[warp * 32 + lane] = v.idx; }
         __syncthreads();
-        if (warp < nw && (warp & (2 * step - 1)) == 0 && warp + step < nw)
+        if (warp < nw && (wg & (2 * step - 1)) == 0 && warp + step < nw)
             v = warp_merge32_shared(v, KeyIdx{ xk[(warp + step) * 32 + lane], xi[(warp + step) * 32 + lane] });
         // no barrier here: a region written at one level is not written again at a later one
     }
@@ -225,8 +227,8 @@ static __device__ __noinline__ KeyIdx cta_tree_merge32_shared(KeyIdx v, uint64_t
     return v;
 }
 template <int NW>
-__device__ __forceinline__ void cta_tree_merge32_rolled(uint64_t &key, uint32_t &idx, uint64_t *xk, uint32_t *xi) {
-    const KeyIdx r = cta_tree_merge32_shared(KeyIdx{ key, idx }, xk, xi, NW);
+__device__ __forceinline__ void cta_tree_merge32_rolled(uint64_t &key, uint32_t &idx, uint64_t *xk, uint32_t *xi, uint32_t group = NW) {
+    const KeyIdx r = cta_tree_merge32_shared(KeyIdx{ key, idx }, xk, xi, NW, group);
     key = r.key; idx = r.idx;
 }
 
@@ -246,9 +248,93 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     __syncthreads();  // lists final, ring idle
     // a CTA whose producers issued no row at all (a very selective label mask) has nothing to sort or merge
     const bool cta_empty = rows_issued && *rows_issued == 0;
-    // 1 + 2. per query: every warp sorts its list, tree merge, warp 0 publishes the CTA's k best
+    // 1 + 2, small batch: the queries' merges are independent, so they run side by side -- NW / nq warps per query, each
+    // sorting and merging nq of the query's NW lists (any warp can read any list: they sit in shared memory), then one
+    // tree per group.  Four queries took four times the single query's 16-level tree before.
+    // 1 + 2 by counting, for short lists: a query's NW*k list entries are n <= a few hundred (key, slot) pairs in shared
+    // memory, all distinct.  One thread per entry counts the entries ahead of it -- the key's high word decides except
+    // between entries that share it, and two keys come with every 128-bit load -- and an entry with fewer than k ahead
+    // of it IS the CTA's entry number `rank`: it goes straight to its place in the published list.  No sort, no
+    // merge tree, one barrier; about n*n/2 compare pairs per query instead of sixteen sorts and four tree levels
+    // (measured on one query, k = 10: 6 us -> see DESIGN.md).  The quadratic cost limits it to small k.
+    const uint32_t n = NW * k;
+    const bool counted = !cta_empty && (n & 1u) == 0 && nq * n * n <= 160000u;
+    if (counted) {
+        __shared__ uint32_t s_valid[4];
+        if (threadIdx.x < 4) s_valid[threadIdx.x] = 0;
+        __syncthreads();
+        uint32_t nvalid[4] = { 0, 0, 0, 0 };
 #pragma unroll 1
-    for (uint32_t qi = 0; qi < nq; qi++) {
+        for (uint32_t c = threadIdx.x; c < nq * n; c += blockDim.x) {
+            const uint32_t qi = c / n, i = c - qi * n;
+            const uint64_t *lk = skeys + qi * qstride;
+            const uint32_t *li = sidx + qi * qstride;
+            const uint64_t mk = lk[i]; const uint32_t mi = li[i];
+            if (mi == kIdxSentinel) continue;
+            nvalid[qi]++;
+            const uint32_t mh = (uint32_t)(mk >> 32);
+            const uint4 *k4 = reinterpret_cast<const uint4 *>(lk);
+            uint32_t lt = 0, eq = 0;
+#pragma unroll 4
+            for (uint32_t j = 0; j < n / 2; j++) {
+                const uint4 v = k4[j];   // {lo, hi} of two keys; the same address in every lane: a broadcast
+                lt += (v.y < mh) + (v.w < mh);
+                eq += (v.y == mh) + (v.w == mh);
+            }
+            uint32_t rank = lt;
+            if (eq > 1) {   // others share the high word (rows without an embedding all score 0): the full comparison
+                rank = 0;
+                for (uint32_t j = 0; j < n; j++) rank += better(lk[j], li[j], mk, mi) ? 1u : 0u;
+            }
+            if (rank < k) {
+                Cand cd; cd.key = mk; cd.idx = mi; cd.pad = 0;
+                a.cta_cands[((size_t)qi * gridDim.x + blockIdx.x) * k + rank] = cd;
+            }
+        }
+#pragma unroll
+        for (uint32_t qi = 0; qi < 4; qi++) {
+            if (qi < nq) {
+                const uint32_t t = __reduce_add_sync(0xffffffffu, nvalid[qi]);
+                if (lane == 0 && t) atomicAdd(&s_valid[qi], t);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < nq * k) {   // fewer than k entries in all: the rest of the published list is padding
+            const uint32_t qi = threadIdx.x / k, r = threadIdx.x - qi * k;
+            if (r >= s_valid[qi]) {
+                Cand cd; cd.key = kKeySentinel; cd.idx = kIdxSentinel; cd.pad = 0;
+                a.cta_cands[((size_t)qi * gridDim.x + blockIdx.x) * k + r] = cd;
+            }
+        }
+        __threadfence();   // every thread's part of the published lists, before the CTA's ticket below
+        __syncthreads();
+    }
+    const bool grouped = !counted && nq > 1 && !cta_empty && (NW % nq) == 0 && ((NW / nq) & (NW / nq - 1)) == 0;
+    if (grouped) {
+        const uint32_t g = NW / nq, qi = warp / g, wg = warp & (g - 1);
+        uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
+        if (warp < NW) {
+#pragma unroll 1
+            for (uint32_t j = 0; j < nq; j++) {
+                const uint32_t src = qi * qstride + (wg * nq + j) * k + lane;
+                uint64_t lk = kKeySentinel; uint32_t li = kIdxSentinel;
+                if (lane < k) { lk = skeys[src]; li = sidx[src]; }
+                warp_sort32_rolled(lk, li, lane, next_pow2(k < 2 ? 2 : k));
+                if (j == 0) { key = lk; idx = li; } else warp_merge32_rolled(key, idx, lk, li, lane);
+            }
+        }
+        cta_tree_merge32_rolled<NW>(key, idx, xk, xi, g);
+        if (warp < NW && wg == 0) {
+            if (lane < k) {
+                Cand c; c.key = key; c.idx = idx; c.pad = 0;
+                a.cta_cands[((size_t)qi * gridDim.x + blockIdx.x) * k + lane] = c;
+            }
+            __threadfence();   // this warp's published list, before the CTA's ticket below
+        }
+        __syncthreads();
+    }
+#pragma unroll 1
+    for (uint32_t qi = 0; qi < (grouped || counted ? 0u : nq); qi++) {
         uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
         if (cta_empty) {
             if (warp == 0 && lane < k) {
@@ -269,14 +355,27 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     if (warp == 0) {   // the only warp that published: its fence, then its ticket -- no block-wide barrier needed before
         __threadfence();
         __syncwarp();
-        if (lane == 0) {
-            const uint32_t ticket = atomicAdd(&a.counters[1], 1u);
-            *s_flag = (ticket == gridDim.x - 1) ? 1u : 0u;
-        }
+        if (lane == 0) *s_flag = atomicAdd(&a.counters[1], 1u);
     }
     __syncthreads();
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 5] = gtime_ns();
-    if (*s_flag == 0) return;
+    // The final merges of a small batch are independent, one per query: instead of the last CTA doing them one after the
+    // other while 147 SMs idle, the last F = min(nq, grid) CTAs to publish take a query each.  The very last one starts
+    // at once; the others first wait until every list is published (all CTAs of a launch are resident or will be -- at
+    // most F - 1 of them wait here -- so the wait ends).  Whichever of the F finishes last re-arms the counters.
+    const uint32_t F = nq < gridDim.x ? nq : gridDim.x;
+    const uint32_t ticket = *s_flag;
+    __syncthreads();   // everyone has read the ticket: s_flag becomes "this CTA wrote the launch's last result"
+    if (threadIdx.x == 0) *s_flag = 0;
+    __syncthreads();
+    if (ticket + F < gridDim.x) return;
+    const uint32_t fin = gridDim.x - 1 - ticket;   // 0 .. F-1: the queries fin, fin + F, ... are this CTA's
+    if (fin != 0) {
+        if (threadIdx.x == 0) {
+            while (*reinterpret_cast<volatile uint32_t *>(&a.counters[1]) < gridDim.x) __nanosleep(100);
+        }
+        __syncthreads();
+    }
     // 3. last CTA, per query: the k best of the gridDim.x published (sorted) lists.
     //
     // Fast path.  Let T be the k-th best of the lists' HEADS (their best entries).  At least k candidates -- those
@@ -294,7 +393,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     uint64_t *hk = xk, *sk = xk + 256;        // heads / survivors live in the (idle) tree-merge exchange buffer
     uint32_t *hi = xi, *si = xi + 256, *hh = xi + 320;   // hh: the heads' high words, 160 entries (16-byte aligned)
 #pragma unroll 1
-    for (uint32_t qi = 0; qi < nq; qi++) {
+    for (uint32_t qi = fin; qi < nq; qi += F) {
         uint64_t key = kKeySentinel; uint32_t idx = kIdxSentinel;
         const Cand *lists = a.cta_cands + (size_t)qi * G * k;
         bool done = false;
@@ -439,8 +538,19 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     }
     if (warp == 0) {
         __syncwarp();
-        if (lane < 2 + nq) a.counters[lane] = 0;
+        uint32_t last = 1;
+        if (F > 1) {   // result writes of this CTA, then its place among the finishers
+            __threadfence();
+            if (lane == 0) last = atomicAdd(&a.counters[6], 1u) == F - 1 ? 1u : 0u;
+            last = __shfl_sync(0xffffffffu, last, 0);
+        }
+        if (last) {
+            if (F > 1) __threadfence();
+            if (lane < 2 + nq || lane == 6) a.counters[lane] = 0;
+            if (lane == 0) *s_flag = 1;
+        }
     }
+    __syncthreads();
 }
 
 // workspace the final merge may use: `ws_entries` (power of two, >= 2*k) entries at ws_keys/ws_idx

@@ -169,7 +169,6 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint32_t s_flag;
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
-    __shared__ uint32_t s_dense;  // small-batch consumers: the producers see most slots pass (see the lazy loop body)
     // consumers with the query in shared memory: the k smallest primary key words (the key's high half: similarity in cosine order, distance
     // in L2 order) any warp of this CTA has offered to its list so far, per query, and the largest of them (see cta_note)
     __shared__ uint32_t s_cta_hi[tma_query_in_smem(V * 128, NQ) ? NQ * 256 : 1];   // k <= 256
@@ -187,7 +186,6 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     if (threadIdx.x == 0) {
         if (a.dbg) a.dbg[blockIdx.x * 8 + 0] = gtime();
         s_seq = 0;
-        s_dense = 0;
         for (uint32_t s = 0; s < NP; s++) { mbar_init(full0 + 8 * s, 2); publish_gen(empty0 + 8 * s, 0); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -283,7 +281,6 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                 const uint32_t len = c & 15u;
                 const uint32_t pick = T * 10u >= 260u * len ? 1u : (T * 10u >= 130u * len ? 2u : (T * 10u >= 16u * len ? 4u : 8u));
                 want = pick < cg ? pick : cg;
-                if (NQ > 1 && lane == 0) s_dense = T * 10u >= 130u * len ? 1u : 0u;   // >= 40 % of the slots pass
             }
             if (T == 0) return;
             __syncwarp();  // clist writes -> reads by other lanes
@@ -530,12 +527,12 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
 #pragma unroll
             for (int j = 0; j < V; j++) { norm4(x[j], pe0); norm4(y[j], pe1); }
             float ev[2] = { pe0.x + pe0.y, pe1.x + pe1.y };
-            if (lazy_ok && *reinterpret_cast<volatile uint32_t *>(&s_dense)) {
-                // ---- lazy body: where most slots pass, the lists are warm and almost no candidate is admitted.  In the
-                // reference's order (similarity first) the distance then only matters for the few that are: score the
-                // dot products alone (a third of the FMAs, half of the reduction), test the similarity against the
-                // list's bound, and compute sum (q-e)^2 -- same per-lane order, same butterfly, hence the same bits as
-                // the full body -- only for a candidate whose similarity does not already rule it out.
+            if (lazy_ok) {
+                // ---- lazy body: with the CTA-wide bound few candidates are admitted.  In the reference's order (similarity
+                // first) the distance then only matters for the few that are: score the dot products alone (a third of
+                // the FMAs, half of the reduction), test the similarity against the bounds, and compute sum (q-e)^2 --
+                // same per-lane order, same butterfly, hence the same bits as the full body -- only for a candidate
+                // whose similarity does not already rule it out.
                 constexpr int NVL = 2 * NQ;          // value index = query * 2 + row
                 constexpr uint32_t TBL = 32 / NVL;   // lane L ends up holding value L / TBL
                 float accl[NVL];
