@@ -82,3 +82,40 @@ def test_identical_queries_in_one_batch_give_identical_lists(corpus):
     out, counts = m.search(qq, 10, mode=sg.MODE_FAST)
     for i in range(1, 4):
         assert counts[i] == counts[0] and out[i].tobytes() == out[0].tobytes()
+
+
+@pytest.mark.parametrize("nq", [1, 2, 4])
+@pytest.mark.parametrize("k", [10, 24, 32])
+def test_ties_on_the_ordering_score_are_broken_by_slot_index(nq, k):
+    """A third of the rows are zero vectors (similarity 0, distance |q|: the whole 64-bit key ties), another block are
+    copies of one row; every other row scores below zero.  The k best are then all ties, spread over every warp's and
+    every CTA's list -- the per-CTA selection by counting and the admission bounds must keep exactly the lowest slot
+    indices, for each query of a batch as for a single one."""
+    n, dim = 30_011, 768
+    rng = np.random.default_rng(31)
+    q = rng.standard_normal((4, dim)).astype(np.float32)
+    q[1:] = q[0] * np.array([[0.5], [2.0], [1.0]], np.float32)          # same direction: one corpus suits all queries
+    E = (-np.abs(rng.standard_normal((n, dim))) * np.sign(q[0])).astype(np.float32)
+    E[::3] = 0.0
+    bloom = np.zeros(n, np.uint64)
+    flags = np.full(n, 7, np.uint8)
+    with sg.Mirror.open_dense(n, dim) as m:
+        m.dense_upload(0, E, bloom, flags)
+        out, counts = m.search(q[:nq], k, mode=sg.MODE_FAST)
+        ref, rc = support.oracle_search_dense(q[:nq], E, bloom, flags, k=k)
+        for i in range(nq):
+            assert counts[i] == rc[i] == k
+            assert np.array_equal(out[i][:k]["slot_idx"], np.arange(0, 3 * k, 3)), (i, out[i][:k]["slot_idx"])
+            support.assert_topk_matches(out[i][:k], ref[i][:k])
+    # copies of the best row: identical (similarity, distance), ranked by slot index
+    E2 = rng.standard_normal((n, dim)).astype(np.float32)
+    best = (q[0] / np.linalg.norm(q[0])).astype(np.float32)
+    where = np.sort(rng.choice(n, 3 * k, replace=False))
+    E2[where] = best
+    with sg.Mirror.open_dense(n, dim) as m:
+        m.dense_upload(0, E2, bloom, flags)
+        out, counts = m.search(q[:nq], k, mode=sg.MODE_FAST)
+        for i in range(nq):
+            assert counts[i] == k
+            assert np.array_equal(out[i][:k]["slot_idx"], where[:k]), (i, out[i][:k]["slot_idx"], where[:k])
+            assert len(set(out[i][:k]["similarity"].tolist())) == 1
