@@ -165,6 +165,7 @@ struct spl_gpu_ctx {
     std::atomic<uint64_t> launches{0};
     bool force_ldg = false;
     bool no_multi = false;  // developer knob SPL_GPU_SCAN_MULTI=0: one query per launch even for small batches
+    bool no_nq8 = false;    // developer knob SPL_GPU_SCAN_NQ8=0: at most four queries per pass
     bool no_overlap = false;  // developer knob SPL_GPU_SCAN_OVERLAP=0: never let a scan start during its predecessor's tail
     unsigned long long *d_dbg = nullptr;  // SPL_GPU_DEBUG_TIMELINE=1: per-CTA timestamps of the last scan
     bool timing = false;
@@ -202,6 +203,7 @@ static int device_setup(spl_gpu_ctx *c, const spl_gpu_opts *o) {
     c->force_ldg = impl && strcmp(impl, "ldg") == 0;
     const char *multi = getenv("SPL_GPU_SCAN_MULTI");
     c->no_multi = multi && strcmp(multi, "0") == 0;
+    { const char *e8 = getenv("SPL_GPU_SCAN_NQ8"); c->no_nq8 = e8 && strcmp(e8, "0") == 0; }
     const char *ovl = getenv("SPL_GPU_SCAN_OVERLAP");
     c->no_overlap = ovl && strcmp(ovl, "0") == 0;
     if (getenv("SPL_GPU_DEBUG_TIMELINE")) {
@@ -960,7 +962,10 @@ static int enqueue_fused(spl_gpu_ctx *c, const spl_gpu_search_params *p, const f
         // for all of them; the rest go one per launch
         uint32_t g = 1;
         if (tma && !c->no_multi) {
-            if (p->nq - qi >= 4 && scan_tma_multi_supported(a.dim, a.k, 4)) g = 4;
+            // eight per pass where only similarities have to be scored for every row (the kernel's lazy loop body)
+            if (p->nq - qi >= 8 && !c->no_nq8 && a.order == SPL_ORDER_COSINE && !(a.max_dist > 0.f) &&
+                scan_tma_multi_supported(a.dim, a.k, 8)) g = 8;
+            else if (p->nq - qi >= 4 && scan_tma_multi_supported(a.dim, a.k, 4)) g = 4;
             else if (p->nq - qi >= 2 && scan_tma_multi_supported(a.dim, a.k, 2)) g = 2;
         }
         a.nq = g;

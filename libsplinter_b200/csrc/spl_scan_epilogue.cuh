@@ -258,12 +258,12 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     // merge tree, one barrier; about n*n/2 compare pairs per query instead of sixteen sorts and four tree levels
     // (measured on one query, k = 10: 6 us -> see DESIGN.md).  The quadratic cost limits it to small k.
     const uint32_t n = NW * k;
-    const bool counted = !cta_empty && (n & 1u) == 0 && nq * n * n <= 160000u;
+    const bool counted = !cta_empty && (n & 1u) == 0 && nq * n * n <= 210000u;
     if (counted) {
-        __shared__ uint32_t s_valid[4];
-        if (threadIdx.x < 4) s_valid[threadIdx.x] = 0;
+        __shared__ uint32_t s_valid[8];
+        if (threadIdx.x < 8) s_valid[threadIdx.x] = 0;
         __syncthreads();
-        uint32_t nvalid[4] = { 0, 0, 0, 0 };
+        uint32_t nvalid[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
 #pragma unroll 1
         for (uint32_t c = threadIdx.x; c < nq * n; c += blockDim.x) {
             const uint32_t qi = c / n, i = c - qi * n;
@@ -271,7 +271,8 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
             const uint32_t *li = sidx + qi * qstride;
             const uint64_t mk = lk[i]; const uint32_t mi = li[i];
             if (mi == kIdxSentinel) continue;
-            nvalid[qi]++;
+#pragma unroll
+            for (uint32_t v = 0; v < 8; v++) nvalid[v] += (qi == v) ? 1u : 0u;   // (constant indices: the counts stay in registers)
             const uint32_t mh = (uint32_t)(mk >> 32);
             const uint4 *k4 = reinterpret_cast<const uint4 *>(lk);
             uint32_t lt = 0, eq = 0;
@@ -292,7 +293,7 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
             }
         }
 #pragma unroll
-        for (uint32_t qi = 0; qi < 4; qi++) {
+        for (uint32_t qi = 0; qi < 8; qi++) {
             if (qi < nq) {
                 const uint32_t t = __reduce_add_sync(0xffffffffu, nvalid[qi]);
                 if (lane == 0 && t) atomicAdd(&s_valid[qi], t);
@@ -541,12 +542,12 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
         uint32_t last = 1;
         if (F > 1) {   // result writes of this CTA, then its place among the finishers
             __threadfence();
-            if (lane == 0) last = atomicAdd(&a.counters[6], 1u) == F - 1 ? 1u : 0u;
+            if (lane == 0) last = atomicAdd(&a.counters[12], 1u) == F - 1 ? 1u : 0u;
             last = __shfl_sync(0xffffffffu, last, 0);
         }
         if (last) {
             if (F > 1) __threadfence();
-            if (lane < 2 + nq || lane == 6) a.counters[lane] = 0;
+            if (lane < 2 + nq || lane == 12) a.counters[lane] = 0;
             if (lane == 0) *s_flag = 1;
         }
     }

@@ -133,7 +133,7 @@ __host__ __device__ inline TmaLayout tma_layout(uint32_t dim, uint32_t k, uint32
     L.clist_off = L.meta_off + kMaxPairs * 16;                    // per producer warp: 256 x {row, flags}
     L.state_off = L.clist_off + kProducers * 256 * 8;             // nq > 1: uint4 per (query, consumer warp)
     const bool qs = tma_query_in_smem(dim, nq) || stage_q;   // stage_q: a query that arrived in the launch's parameter space
-    L.q_off = L.state_off + (qs ? nq * kConsumers * 20u + 16u : 0u);  // + u32 survivors per list, |q|^2 per query
+    L.q_off = L.state_off + (qs ? nq * kConsumers * 20u + ((nq * 4u + 15u) & ~15u) : 0u);  // + u32 survivors per list, |q|^2 per query
                                                                   // then the queries, fp32 [nq][dim]
     L.rows_off = (L.q_off + (qs ? nq * L.row_bytes : 0u) + 127u) & ~127u;
     const uint32_t avail = kSmemBudget - 8192u - L.rows_off;      // 8 KB headroom for static smem
@@ -171,8 +171,9 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
     __shared__ uint32_t s_seq;  // rows issued so far by all producer warps
     // consumers with the query in shared memory: the k smallest primary key words (the key's high half: similarity in cosine order, distance
     // in L2 order) any warp of this CTA has offered to its list so far, per query, and the largest of them (see cta_note)
-    __shared__ uint32_t s_cta_hi[tma_query_in_smem(V * 128, NQ) ? NQ * 256 : 1];   // k <= 256
-    __shared__ uint32_t s_cta_kth[4];
+    constexpr uint32_t kCtaHi = !tma_query_in_smem(V * 128, NQ) ? 1u : (NQ == 8 ? 8u * 32u : (uint32_t)NQ * 256u);   // NQ = 8: k <= 32
+    __shared__ uint32_t s_cta_hi[kCtaHi];
+    __shared__ uint32_t s_cta_kth[8];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const TmaLayout L = tma_layout(a.dim, a.k, NQ, QP);
     const uint32_t list_entries = L.list_entries;
@@ -197,8 +198,8 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
             wstate[i] = make_uint4((uint32_t)kKeySentinel, (uint32_t)(kKeySentinel >> 32), kIdxSentinel, 0u);
             reinterpret_cast<uint32_t *>(wstate + NQ * kConsumers)[i] = 0u;
         }
-        for (uint32_t i = threadIdx.x; i < NQ * 256; i += blockDim.x) s_cta_hi[i] = 0xffffffffu;
-        if (threadIdx.x < 4) s_cta_kth[threadIdx.x] = 0xffffffffu;
+        for (uint32_t i = threadIdx.x; i < kCtaHi; i += blockDim.x) s_cta_hi[i] = 0xffffffffu;
+        if (threadIdx.x < 8) s_cta_kth[threadIdx.x] = 0xffffffffu;
         float4 *sq4 = reinterpret_cast<float4 *>(smem + L.q_off);
         const float4 *gq4 = reinterpret_cast<const float4 *>(a.q);
         for (uint32_t i = threadIdx.x; i < NQ * (a.dim >> 2); i += blockDim.x) sq4[i] = gq4[i];
@@ -735,7 +736,8 @@ bool scan_tma_supported(uint32_t dim, uint32_t k) {
 
 // small-batch variant: nq in {2, 4} queries per pass, register/shuffle epilogue only (k <= 32)
 bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq) {
-    if (nq != 2 && nq != 4) return false;
+    if (nq != 2 && nq != 4 && nq != 8) return false;
+    if (nq == 8 && (k > 32 || dim > 768)) return false;   // eight queries: the register/shuffle epilogue, rows of up to 768 floats
     if (k == 0 || k > 256 || !scan_tma_supported(dim, k)) return false;
     const TmaLayout L = tma_layout(dim, k, nq);
     return L.pairs >= kMinPairs;
@@ -769,6 +771,7 @@ static cudaError_t launch_nq(const ScanArgs &a, int grid, cudaStream_t stream) {
         case 0: case 1: return launch_v<V, 1>(a, grid, stream);
         case 2: return launch_v<V, 2>(a, grid, stream);
         case 4: return launch_v<V, 4>(a, grid, stream);
+        case 8: return launch_v<V, 8>(a, grid, stream);
         default: return cudaErrorInvalidValue;
     }
 }
@@ -778,7 +781,8 @@ static cudaError_t prepare_v(int bytes) {
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(scan_tma_kernel<V, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
     if ((e = cudaFuncSetAttribute(scan_tma_kernel<V, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
-    return cudaFuncSetAttribute(scan_tma_kernel<V, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if ((e = cudaFuncSetAttribute(scan_tma_kernel<V, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    return cudaFuncSetAttribute(scan_tma_kernel<V, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 // opt in to > 48 KB dynamic shared memory; call once per device with that device current

@@ -1,4 +1,4 @@
-"""Small-batch scans: 2 or 4 queries share one pass over the store (spl_scan_tma.cu, NQ > 1), so each row
+"""Small-batch scans: 2, 4 or 8 queries share one pass over the store (spl_scan_tma.cu, NQ > 1), so each row
 fetched from HBM is scored for all of them.  Same contract as the single-query scan; the per-row
 arithmetic is the same instruction sequence, so a batch must return bit-for-bit what the same queries
 return one at a time, and both must match the CPU oracle."""
@@ -21,11 +21,11 @@ def _mirror(n, dim, seed=1234):
 @pytest.fixture(scope="module")
 def corpus():
     m, E, bloom, flags = _mirror(40_003, 768)
-    yield m, E, bloom, flags, support.synth_queries(777, 8, 768)
+    yield m, E, bloom, flags, support.synth_queries(777, 16, 768)
     m.close()
 
 
-@pytest.mark.parametrize("nq", [2, 3, 4, 5, 7, 8])
+@pytest.mark.parametrize("nq", [2, 3, 4, 5, 7, 8, 9, 13, 16])
 @pytest.mark.parametrize("k", [1, 10, 32, 33, 100, 256])
 def test_batch_equals_one_at_a_time_and_the_oracle(corpus, nq, k):
     m, E, bloom, flags, q = corpus
@@ -84,7 +84,7 @@ def test_identical_queries_in_one_batch_give_identical_lists(corpus):
         assert counts[i] == counts[0] and out[i].tobytes() == out[0].tobytes()
 
 
-@pytest.mark.parametrize("nq", [1, 2, 4])
+@pytest.mark.parametrize("nq", [1, 2, 4, 8])
 @pytest.mark.parametrize("k", [10, 24, 32])
 def test_ties_on_the_ordering_score_are_broken_by_slot_index(nq, k):
     """A third of the rows are zero vectors (similarity 0, distance |q|: the whole 64-bit key ties), another block are
@@ -93,8 +93,8 @@ def test_ties_on_the_ordering_score_are_broken_by_slot_index(nq, k):
     indices, for each query of a batch as for a single one."""
     n, dim = 30_011, 768
     rng = np.random.default_rng(31)
-    q = rng.standard_normal((4, dim)).astype(np.float32)
-    q[1:] = q[0] * np.array([[0.5], [2.0], [1.0]], np.float32)          # same direction: one corpus suits all queries
+    q = rng.standard_normal((8, dim)).astype(np.float32)
+    q[1:] = q[0] * np.array([[0.5], [2.0], [1.0], [0.25], [4.0], [1.5], [3.0]], np.float32)   # same direction: one corpus suits all
     E = (-np.abs(rng.standard_normal((n, dim))) * np.sign(q[0])).astype(np.float32)
     E[::3] = 0.0
     bloom = np.zeros(n, np.uint64)
@@ -119,3 +119,19 @@ def test_ties_on_the_ordering_score_are_broken_by_slot_index(nq, k):
             assert counts[i] == k
             assert np.array_equal(out[i][:k]["slot_idx"], where[:k]), (i, out[i][:k]["slot_idx"], where[:k])
             assert len(set(out[i][:k]["similarity"].tolist())) == 1
+
+
+def test_eight_per_pass_with_a_similarity_threshold_and_exclusion(corpus):
+    """Cosine order without a distance threshold is what the 8-queries-per-pass kernel takes (11 queries = 8 + 2 + 1);
+    a similarity threshold cuts inside the candidates and one slot is excluded."""
+    m, E, bloom, flags, q = corpus
+    kw = dict(bloom_mask=0x2, min_similarity=0.02, exclude_slot=17)
+    out, counts = m.search(q[:11], 16, mode=sg.MODE_FAST, **kw)
+    ref, rc = support.oracle_search_dense(q[:11], E, bloom, flags, k=16, bloom_mask=0x2, min_sim=0.02, exclude=17)
+    full, fc = support.oracle_search_dense(q[:11], E, bloom, flags, k=0, bloom_mask=0x2, min_sim=0.02, exclude=17)
+    totals = m.last_totals(11)
+    for i in range(11):
+        one, c1 = m.search(q[i], 16, mode=sg.MODE_FAST, **kw)
+        assert out[i][:counts[i]].tobytes() == one[0][:c1[0]].tobytes()
+        support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
+        assert abs(int(totals[i]) - int(fc[i])) <= 2      # rows sitting within an ulp of the threshold
