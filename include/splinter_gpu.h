@@ -48,7 +48,7 @@ typedef struct spl_gpu_ctx spl_gpu_ctx;
 #define SPL_ORDER_L2     1u /* distance asc, similarity desc, idx asc (batched L2 config) */
 
 /* ---- compute mode ------------------------------------------------------------------ */
-#define SPL_MODE_AUTO    0u /* FAST (small batches share passes 4 or 2 queries at a time); BATCH_BF16 from 16 queries up
+#define SPL_MODE_AUTO    0u /* FAST (small batches share passes 8, 4 or 2 queries at a time); BATCH_BF16 from 16 queries up
                                (from 4 when no label mask is given) if a bf16 mirror exists and no threshold is set on
                                the score that does not order the result */
 #define SPL_MODE_FAST    1u /* fp32, per-lane partial sums + warp-shuffle tree (|d sim| ~1e-6)           */

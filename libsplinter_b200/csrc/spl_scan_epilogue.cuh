@@ -162,7 +162,7 @@ __device__ __forceinline__ void scan_epilogue_small(const ScanArgs &a, uint64_t 
     }
 }
 
-// ---- compact epilogue for k <= 32 (TMA scan kernel; nq = 1, 2 or 4 queries) ------------------------------
+// ---- compact epilogue for k <= 32 (TMA scan kernel; nq = 1, 2, 4 or 8 queries) ------------------------------
 // Same three steps as scan_epilogue_small, written as ROLLED loops around one instance of each building block.
 // The epilogue runs once per CTA, so its instructions are always cold: measured, the time of the unrolled
 // version (~30 KB of straight-line code per query) was mostly instruction fetch, about 0.45 us per KB.
@@ -362,8 +362,11 @@ __device__ __forceinline__ void scan_epilogue_compact(const ScanArgs &a, uint32_
     if (a.dbg && threadIdx.x == 0) a.dbg[blockIdx.x * 8 + 5] = gtime_ns();
     // The final merges of a small batch are independent, one per query: instead of the last CTA doing them one after the
     // other while 147 SMs idle, the last F = min(nq, grid) CTAs to publish take a query each.  The very last one starts
-    // at once; the others first wait until every list is published (all CTAs of a launch are resident or will be -- at
-    // most F - 1 of them wait here -- so the wait ends).  Whichever of the F finishes last re-arms the counters.
+    // at once; the others first wait until every list is published.  The wait ends: a launch never has more than F - 1
+    // <= 7 CTAs waiting here, every other CTA runs to its exit without waiting for anything, so the CTAs still to come
+    // always find an SM (it would take some twenty small-batch launches in flight on one GPU at once -- each context
+    // runs its searches one after another -- for the waiters to hold every SM).  Whichever of the F finishes last
+    // re-arms the counters.
     const uint32_t F = nq < gridDim.x ? nq : gridDim.x;
     const uint32_t ticket = *s_flag;
     __syncthreads();   // everyone has read the ticket: s_flag becomes "this CTA wrote the launch's last result"

@@ -1,4 +1,4 @@
-// spl_scan_tma.cu -- fused scan, TMA-staged (the default SPL_MODE_FAST kernel): one query, or 2 / 4 queries per pass.
+// spl_scan_tma.cu -- fused scan, TMA-staged (the default SPL_MODE_FAST kernel): one query, or 2 / 4 / 8 queries per pass.
 //
 // Same contract as spl_scan.cu (predicate -> cosine + L2 -> thresholds -> top-k; reference:
 // /root/reference/splinter_cli_cmd_search.c:336-416) but the embedding rows travel HBM -> shared
@@ -13,7 +13,7 @@
 //                     registers with conflict-free 128-bit LDS, hand the slot back, then score the two rows
 //                     (dot, |e|^2, sum (q-e)^2 with packed FFMA2, warp-shuffle tree) and feed the per-warp
 //                     top-k list.  NQ = 1: the query sits in registers (in shared memory for 1024-d rows).
-//                     NQ = 2 / 4: the queries sit in shared memory, every row is scored against each of them,
+//                     NQ = 2 / 4 / 8: the queries sit in shared memory, every row is scored against each of them,
 //                     the partial sums are reduced transposed and each (query, row) is finished by its own lane.
 //
 // One persistent CTA per SM keeps up to ~190 KB of row data in flight per SM no matter what the
@@ -734,7 +734,7 @@ bool scan_tma_supported(uint32_t dim, uint32_t k) {
     return tma_layout(dim, k).pairs >= kMinPairs;
 }
 
-// small-batch variant: nq in {2, 4} queries per pass, register/shuffle epilogue only (k <= 32)
+// small-batch variant: nq in {2, 4, 8} queries per pass
 bool scan_tma_multi_supported(uint32_t dim, uint32_t k, uint32_t nq) {
     if (nq != 2 && nq != 4 && nq != 8) return false;
     if (nq == 8 && (k > 32 || dim > 768)) return false;   // eight queries: the register/shuffle epilogue, rows of up to 768 floats
