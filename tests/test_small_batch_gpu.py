@@ -63,14 +63,16 @@ def test_exact_mode_rides_the_same_batched_scan(corpus):
         support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]], exact=True)
 
 
-@pytest.mark.parametrize("dim", [1024, 512, 128])
-def test_other_dims_and_no_candidates(dim):
+@pytest.mark.parametrize("dim", [1024, 512, 256, 128])
+@pytest.mark.parametrize("nq", [4, 8])
+def test_other_dims_and_no_candidates(dim, nq):
+    """(eight per pass exists for rows of up to 768 floats; 1024-d batches of eight go four at a time)"""
     m, E, bloom, flags = _mirror(9_001, dim, seed=5)
-    q = support.synth_queries(11, 4, dim)
+    q = support.synth_queries(11, nq, dim)
     for mask in (0, 1 << 63, (1 << 64) - 1):
         out, counts = m.search(q, 10, mode=sg.MODE_FAST, bloom_mask=mask)
         ref, rc = support.oracle_search_dense(q, E, bloom, flags, k=10, bloom_mask=mask)
-        for i in range(4):
+        for i in range(nq):
             assert counts[i] == rc[i]
             support.assert_topk_matches(out[i][:counts[i]], ref[i][:rc[i]])
     m.close()
