@@ -85,9 +85,33 @@ __device__ __forceinline__ unsigned long long gtime() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+// L2 residency: a query streams hundreds of MB of rows through a 126 MB L2 once and never looks at them again, while the
+// 9 bytes per slot of predicate data (bloom + flags, 9.4 MB at 2^20 slots) are read again by every query.  The rows are
+// therefore fetched evict-first and the predicate bytes evict-last: the predicate columns stay in L2 from one query to
+// the next instead of being pushed out by rows on their way to nowhere.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t ldg_u64_hint(const uint64_t *ptr, uint64_t policy) {
+    uint64_t v;
+    asm volatile("ld.global.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(ptr), "l"(policy));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldg_u8_hint(const uint8_t *ptr, uint64_t policy) {
+    uint32_t v;
+    asm volatile("ld.global.L2::cache_hint.u8 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(policy));
+    return v;
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
 }
 
 // Packed fp32 pairs (FFMA2, sm_100): one instruction does the (x, y) or (z, w) half of a float4.  Every sum below
@@ -228,6 +252,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
         const uint32_t ngroups = (a.n + 31u) >> 5;
         const unsigned char *Eb = reinterpret_cast<const unsigned char *>(a.E);
         const uint32_t rows_s = smem_u32(smem + L.rows_off);
+        const uint64_t pol_keep = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
         // Work is handed out in chunks of kChunk groups (kChunk*32 slots) by one atomic per chunk
         // (a single counter cannot sustain one atomic per 32 slots at HBM speed).  The NEXT chunk's
         // base and its predicate bytes are requested before the current chunk's rows are issued, so
@@ -257,7 +282,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
             for (int j = 0; j < kChunk; j++) {
                 const uint32_t row = ((g0 + j) << 5) + lane;   // g0 < 2^27, so this cannot wrap
                 f[j] = 0; b[j] = 0;
-                if (j < len && g0 + j < ngroups && row < a.n) { f[j] = a.flags[row]; b[j] = a.bloom[row]; }
+                if (j < len && g0 + j < ngroups && row < a.n) { f[j] = ldg_u8_hint(a.flags + row, pol_keep); b[j] = ldg_u64_hint(a.bloom + row, pol_keep); }
             }
         };
         // Rows that pass are first compacted into a per-warp list in shared memory, then issued 32 at a
@@ -306,7 +331,7 @@ __device__ __forceinline__ void scan_tma_body(const ScanArgs &a, const float4 *q
                     meta32[slot * 4 + sub * 2 + 1] = me.y;
                     if (bytes) {
                         mbar_arrive_expect_tx(fullb, bytes);
-                        bulk_g2s(rows_s + (slot * 2 + sub) * RB, Eb + (size_t)me.x * RB, bytes, fullb);
+                        bulk_g2s(rows_s + (slot * 2 + sub) * RB, Eb + (size_t)me.x * RB, bytes, fullb, pol_stream);
                     } else {
                         mbar_arrive(fullb);
                     }
