@@ -300,11 +300,15 @@ def run_ours(args):
         qbuf = torch.empty(DIM, dtype=torch.float32, device=dev)
         hp = m.params(1, k, mode=sg.MODE_AUTO, bloom_mask=mask)
         h_out, h_cnt = np.zeros((1, k), sg.RESULT_DTYPE), np.zeros(1, np.uint32)
+        # what a C host holds: plain addresses (numpy's .ctypes accessors cost about a microsecond each)
+        import ctypes
+        hp_ref, q_addr = ctypes.byref(hp), [q_host[i].ctypes.data for i in range(N_QUERIES)]
+        out_addr, cnt_addr = h_out.ctypes.data, h_cnt.ctypes.data
 
         def one(i):
             if single:
                 # the host-buffer C-ABI call itself: query in host memory in, records in host memory out
-                m.search_into(hp, q_host[i % N_QUERIES], h_out, k, h_cnt)
+                m.search_ptrs(hp_ref, q_addr[i % N_QUERIES], out_addr, k, cnt_addr)
             else:
                 qbuf.copy_(q_pin[i % N_QUERIES], non_blocking=True)
                 device_step(i, mask, qsrc=qbuf)

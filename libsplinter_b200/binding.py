@@ -309,6 +309,13 @@ class Mirror:
         if rc != 0:
             self._check(rc)
 
+    def search_ptrs(self, p_ref, q_addr: int, out_addr: int, out_stride: int, counts_addr: int):
+        """spl_gpu_search on raw host addresses (p_ref = ctypes.byref(params), made once): nothing but the C call, for
+        loops that would otherwise time numpy's `.ctypes` accessors (about a microsecond each) along with it"""
+        rc = self._lib.spl_gpu_search(self._h, p_ref, q_addr, out_addr, out_stride, counts_addr)
+        if rc != 0:
+            self._check(rc)
+
     def search_device(self, p: SearchParams, d_q: int, d_out: int, out_stride: int, d_counts: int, stream: int = 0):
         self._check(self._lib.spl_gpu_search_device(self._h, C.byref(p), C.c_void_p(d_q), C.c_void_p(d_out),
                                                     out_stride, C.c_void_p(d_counts), C.c_void_p(stream)))
